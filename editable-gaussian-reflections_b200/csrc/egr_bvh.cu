@@ -1,0 +1,398 @@
+// LBVH over per-Gaussian bounding proxies: Morton codes + radix sort + Karras topology, stored in DFS preorder
+// with skip indices (stackless traversal), refit bottom-up every iteration or after an edit.
+// Replaces the reference's opaque OptiX instance acceleration structure
+// (editable_gauss_refl/cuda/csrc/optix/bvh_wrapper.h:24-157, bvh_wrapper.cu:9-70).
+#include <cub/device/device_radix_sort.cuh>
+
+#include "egr_common.cuh"
+
+namespace egr {
+
+// ---------------------------------------------------------------------------------------------------------
+// Build scratch layout
+// ---------------------------------------------------------------------------------------------------------
+struct BuildScratch {
+    size_t keys_in, keys_out, ids_in, child_l, child_r, parent_int, parent_leaf, first, last, cub_temp, total;
+    size_t cub_bytes;
+};
+static BuildScratch build_scratch_layout(uint32_t n) {
+    BuildScratch L;
+    size_t o = 0;
+    L.keys_in = o, o = align_up(o + (size_t)n * 8, 256);
+    L.keys_out = o, o = align_up(o + (size_t)n * 8, 256);
+    L.ids_in = o, o = align_up(o + (size_t)n * 4, 256);
+    L.child_l = o, o = align_up(o + (size_t)n * 4, 256);
+    L.child_r = o, o = align_up(o + (size_t)n * 4, 256);
+    L.parent_int = o, o = align_up(o + (size_t)n * 4, 256);
+    L.parent_leaf = o, o = align_up(o + (size_t)n * 4, 256);
+    L.first = o, o = align_up(o + (size_t)n * 4, 256);
+    L.last = o, o = align_up(o + (size_t)n * 4, 256);
+    size_t cub = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, cub, (const uint64_t *)nullptr, (uint64_t *)nullptr,
+                                    (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)n, 0, 64);
+    L.cub_bytes = cub;
+    L.cub_temp = o, o = align_up(o + cub, 256);
+    L.total = o;
+    return L;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Kernels
+// ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float atomicMinFloat(float *addr, float v) {
+    // valid for any mix of signs: ints order like floats for >=0, reversed for <0
+    return v >= 0 ? __int_as_float(atomicMin((int *)addr, __float_as_int(v)))
+                  : __uint_as_float(atomicMax((unsigned *)addr, __float_as_uint(v)));
+}
+__device__ __forceinline__ float atomicMaxFloat(float *addr, float v) {
+    return v >= 0 ? __int_as_float(atomicMax((int *)addr, __float_as_int(v)))
+                  : __uint_as_float(atomicMin((unsigned *)addr, __float_as_uint(v)));
+}
+
+__global__ void k_bounds_init(float *bounds) {
+    if (threadIdx.x < 3) bounds[threadIdx.x] = 3.0e38f;
+    else if (threadIdx.x < 6) bounds[threadIdx.x] = -3.0e38f;
+}
+
+__global__ void __launch_bounds__(256) k_bounds(const float *__restrict__ mean, uint32_t n, float *bounds) {
+    float mn[3] = {3.0e38f, 3.0e38f, 3.0e38f}, mx[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            float v = mean[3 * (size_t)i + c];
+            if (isfinite(v)) mn[c] = fminf(mn[c], v), mx[c] = fmaxf(mx[c], v);
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            mn[c] = fminf(mn[c], __shfl_xor_sync(0xffffffffu, mn[c], o));
+            mx[c] = fmaxf(mx[c], __shfl_xor_sync(0xffffffffu, mx[c], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            atomicMinFloat(&bounds[c], mn[c]);
+            atomicMaxFloat(&bounds[3 + c], mx[c]);
+        }
+    }
+}
+
+__device__ __forceinline__ uint64_t expand21(uint32_t v) {  // spread 21 bits to every third bit
+    uint64_t x = v & 0x1fffffu;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+// 63-bit Morton code of the mean on a 2^21 grid over the scene bounds (integer-exact given the bounds).
+__global__ void __launch_bounds__(256)
+k_morton(const float *__restrict__ mean, uint32_t n, const float *__restrict__ bounds, uint64_t *keys, uint32_t *ids) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t q[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        float lo = bounds[c], hi = bounds[3 + c];
+        float ext = hi - lo;
+        float v = mean[3 * (size_t)i + c];
+        float u = ext > 0.0f ? (v - lo) / ext : 0.0f;
+        u = isfinite(u) ? fminf(fmaxf(u, 0.0f), 1.0f) : 0.0f;
+        q[c] = min((uint32_t)(u * 2097152.0f), 2097151u);
+    }
+    keys[i] = (expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2]);
+    ids[i] = i;
+}
+
+// delta(i,j): length of the common prefix of the (key, index) pairs; -1 outside the range (Karras 2012).
+__device__ __forceinline__ int delta(const uint64_t *__restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz((uint32_t)i ^ (uint32_t)j);
+    return __clzll((long long)(a ^ b));
+}
+
+// One thread per internal node i in [0, n-2].  Children are encoded as (index << 1 | is_leaf).
+__global__ void __launch_bounds__(256)
+k_karras(const uint64_t *__restrict__ keys, int n, uint32_t *child_l, uint32_t *child_r, uint32_t *parent_int,
+         uint32_t *parent_leaf, uint32_t *first, uint32_t *last) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + min(d, 0);
+    int lo = min(i, j), hi = max(i, j);
+    bool l_leaf = lo == gamma, r_leaf = hi == gamma + 1;
+    child_l[i] = ((uint32_t)gamma << 1) | (l_leaf ? 1u : 0u);
+    child_r[i] = ((uint32_t)(gamma + 1) << 1) | (r_leaf ? 1u : 0u);
+    if (l_leaf) parent_leaf[gamma] = i; else parent_int[gamma] = i;
+    if (r_leaf) parent_leaf[gamma + 1] = i; else parent_int[gamma + 1] = i;
+    first[i] = lo, last[i] = hi;
+    if (i == 0) parent_int[0] = NO_PARENT;
+}
+
+// DFS preorder index of a node = 2*first_leaf + (number of left turns on the path from the root); found by walking
+// up.  Threads [0, n-1) handle internal nodes, [n-1, 2n-1) handle leaves.  Writes topology fields of the node.
+__global__ void __launch_bounds__(256)
+k_preorder(int n, const uint32_t *__restrict__ child_l, const uint32_t *__restrict__ parent_int,
+           const uint32_t *__restrict__ parent_leaf, const uint32_t *__restrict__ first,
+           const uint32_t *__restrict__ last, float4 *nodes, uint32_t *parents, uint32_t *leaf_node, uint32_t *flags) {
+    int tid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tid >= 2 * n - 1) return;
+    bool is_leaf = tid >= n - 1;
+    uint32_t idx = is_leaf ? tid - (n - 1) : tid;
+    uint32_t a = is_leaf ? idx : first[idx];
+    uint32_t nl = is_leaf ? 1u : last[idx] - first[idx] + 1u;
+    uint32_t turns = 0;
+    uint32_t cur_code = (idx << 1) | (is_leaf ? 1u : 0u);
+    uint32_t p = is_leaf ? (n > 1 ? parent_leaf[idx] : NO_PARENT) : parent_int[idx];
+    uint32_t direct_parent = p;
+    uint32_t first_turn = 0;
+    bool first_iter = true;
+    while (p != NO_PARENT) {
+        uint32_t t = child_l[p] == cur_code ? 1u : 0u;
+        if (first_iter) first_turn = t, first_iter = false;
+        turns += t;
+        cur_code = p << 1;
+        p = parent_int[p];
+    }
+    uint32_t pre = 2u * a + turns;
+    uint32_t skip = pre + 2u * nl - 1u;
+    uint32_t ppre = direct_parent == NO_PARENT ? NO_PARENT : 2u * first[direct_parent] + (turns - first_turn);
+    nodes[2 * (size_t)pre] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(skip));       // empty box until refit
+    nodes[2 * (size_t)pre + 1] = make_float4(-1.0f, -1.0f, -1.0f, __uint_as_float(is_leaf ? idx : INTERNAL));
+    parents[pre] = ppre;
+    flags[pre] = 0;
+    if (is_leaf) leaf_node[idx] = pre;
+}
+
+// Geometry record + leaf box for leaf j, then bottom-up box propagation (second arrival continues upward).
+// Reference for the per-Gaussian math: bvh_wrapper.cu:9-59 (_populateBVH), utils/kernel.cu:3-6,
+// utils/activations.cu:5,59,67-69.  The reference's three host syncs (bvh_wrapper.h:38-40) are gone: the config
+// scalars are read here through their device pointers.
+__global__ void __launch_bounds__(256) k_refit(BvhView bvh, EgrGaussians g, EgrConfig cfg) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= bvh.n) return;
+    const float alpha_threshold = *cfg.alpha_threshold, exp_power = *cfg.exp_power, gsf = *cfg.global_scale_factor;
+    const uint32_t id = bvh.sorted_ids[j];
+    const float k = 2.0f * exp_power;
+    float sigma = 1.0f / (1.0f + expf(-g.opacity[id]));
+    float sf = sigma <= alpha_threshold ? 0.0f : powf(k * logf(sigma / alpha_threshold), 1.0f / k);
+    f3 s = mk3(expf(g.scale[3 * (size_t)id]), expf(g.scale[3 * (size_t)id + 1]), expf(g.scale[3 * (size_t)id + 2]));
+    f3 S = s * sf * gsf;
+    const float4 q4 = reinterpret_cast<const float4 *>(g.rotation)[id];
+    float r = q4.x, x = q4.y, y = q4.z, z = q4.w;
+    float norm = sqrtf(r * r + x * x + y * y + z * z);
+    r /= norm, x /= norm, y /= norm, z /= norm;
+    float R[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+                     {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+                     {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+    f3 mu = ld3(g.mean, id);
+    bool visible = sf > 0.0f && S.x > 0.0f && S.y > 0.0f && S.z > 0.0f && isfinite(norm) && norm > 0.0f &&
+                   isfinite(mu.x) && isfinite(mu.y) && isfinite(mu.z) && isfinite(S.x) && isfinite(S.y) && isfinite(S.z);
+    float Sv[3] = {S.x, S.y, S.z};
+    float4 rec[3];
+    float *rf = reinterpret_cast<float *>(rec);
+    float muv[3] = {mu.x, mu.y, mu.z};
+#pragma unroll
+    for (int rr = 0; rr < 3; ++rr) {
+#pragma unroll
+        for (int c = 0; c < 3; ++c) rf[4 * rr + c] = visible ? R[c][rr] / Sv[rr] : 0.0f;
+        rf[4 * rr + 3] = muv[rr];
+    }
+    bvh.records[4 * (size_t)j + 0] = rec[0];
+    bvh.records[4 * (size_t)j + 1] = rec[1];
+    bvh.records[4 * (size_t)j + 2] = rec[2];
+    bvh.records[4 * (size_t)j + 3] = make_float4(sf, sigma, __uint_as_float(id), visible ? 1.0f : 0.0f);
+
+    // world box of the image of [-1,1]^3 under M = R diag(S), inflated so that it is strictly conservative w.r.t.
+    // the exact local-space test (which alone defines the candidate set)
+    float bmin[3], bmax[3];
+#pragma unroll
+    for (int rr = 0; rr < 3; ++rr) {
+        float e = fabsf(R[rr][0]) * S.x + fabsf(R[rr][1]) * S.y + fabsf(R[rr][2]) * S.z;
+        e = e * 1.00002f + 1.0e-6f * (fabsf(muv[rr]) + e) + 1.0e-30f;
+        bmin[rr] = visible ? muv[rr] - e : 1.0f;
+        bmax[rr] = visible ? muv[rr] + e : -1.0f;
+    }
+    uint32_t node = bvh.leaf_node[j];
+    uint32_t skip = node + 1;
+    bvh.nodes[2 * (size_t)node] = make_float4(bmin[0], bmin[1], bmin[2], __uint_as_float(skip));
+    bvh.nodes[2 * (size_t)node + 1] = make_float4(bmax[0], bmax[1], bmax[2], __uint_as_float(j));
+
+    uint32_t p = bvh.parents[node];
+    while (p != NO_PARENT) {
+        __threadfence();
+        uint32_t old = atomicAdd(&bvh.flags[p], 1u);
+        if (old == 0) return;  // first arrival: the sibling subtree is not finished yet
+        bvh.flags[p] = 0;      // second (last) arrival re-arms the counter for the next refit
+        uint32_t lc = p + 1;
+        float4 la = __ldcg(&bvh.nodes[2 * (size_t)lc]), lb = __ldcg(&bvh.nodes[2 * (size_t)lc + 1]);
+        uint32_t rc = __float_as_uint(la.w);  // right child = skip of the left child
+        float4 ra = __ldcg(&bvh.nodes[2 * (size_t)rc]), rb = __ldcg(&bvh.nodes[2 * (size_t)rc + 1]);
+        bool le = la.x > lb.x, re = ra.x > rb.x;  // empty boxes (invisible subtrees)
+        float4 a, b;
+        if (le && re) {
+            a = make_float4(1.0f, 1.0f, 1.0f, 0.0f), b = make_float4(-1.0f, -1.0f, -1.0f, 0.0f);
+        } else if (le) {
+            a = ra, b = rb;
+        } else if (re) {
+            a = la, b = lb;
+        } else {
+            a = make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), 0.0f);
+            b = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), 0.0f);
+        }
+        float4 pa = __ldcg(&bvh.nodes[2 * (size_t)p]);
+        a.w = pa.w;  // keep skip
+        b.w = __uint_as_float(INTERNAL);
+        __stcg(&bvh.nodes[2 * (size_t)p], a);
+        __stcg(&bvh.nodes[2 * (size_t)p + 1], b);
+        p = bvh.parents[p];
+    }
+}
+
+// Activated appearance, permuted to leaf order; runs at the start of every raytrace() so that colour / BRDF edits
+// take effect without a refit, as in the reference where the programs read the parameters directly
+// (csrc/utils/helpers.cu:21-33).
+__global__ void __launch_bounds__(256) k_pack_appearance(BvhView bvh, EgrGaussians g) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= bvh.n) return;
+    const uint32_t id = bvh.sorted_ids[j];
+    f3 rgb = ld3(g.rgb, id), nrm = ld3(g.normal, id), f0 = ld3(g.f0, id);
+    float rough = g.roughness[id];
+    rgb = mk3(fmaxf(0.0f, rgb.x), fmaxf(0.0f, rgb.y), fmaxf(0.0f, rgb.z));
+    f0 = mk3(fminf(fmaxf(0.0f, f0.x), 1.0f), fminf(fmaxf(0.0f, f0.y), 1.0f), fminf(fmaxf(0.0f, f0.z), 1.0f));
+    rough = fminf(fmaxf(0.0f, rough), 1.0f);
+    bvh.appearance[3 * (size_t)j + 0] = make_float4(rgb.x, rgb.y, rgb.z, rough);
+    bvh.appearance[3 * (size_t)j + 1] = make_float4(nrm.x, nrm.y, nrm.z, 0.0f);
+    bvh.appearance[3 * (size_t)j + 2] = make_float4(f0.x, f0.y, f0.z, 0.0f);
+}
+
+int launch_pack_appearance(const BvhView &bvh, const EgrGaussians &g, cudaStream_t st) {
+    if (bvh.n == 0) return EGR_OK;
+    k_pack_appearance<<<(bvh.n + 255) / 256, 256, 0, st>>>(bvh, g);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}
+
+}  // namespace egr
+
+using namespace egr;
+
+extern "C" size_t egr_bvh_storage_bytes(uint32_t n) { return bvh_layout(n).total; }
+extern "C" size_t egr_bvh_scratch_bytes(uint32_t n) { return build_scratch_layout(n).total; }
+
+static int check_gaussians(const EgrGaussians *g) {
+    if (!g) {
+        set_error("gaussians is null");
+        return EGR_EINVAL;
+    }
+    if (g->count && (!g->rgb || !g->normal || !g->f0 || !g->roughness || !g->opacity || !g->scale || !g->mean ||
+                     !g->rotation)) {
+        set_error("gaussians: null parameter pointer with count=%u", g->count);
+        return EGR_EINVAL;
+    }
+    if (((uintptr_t)g->rotation & 15) != 0) {
+        set_error("gaussians.rotation must be 16-byte aligned");
+        return EGR_EINVAL;
+    }
+    return EGR_OK;
+}
+
+extern "C" int egr_bvh_refit(const EgrGaussians *g, const EgrConfig *cfg, void *storage, size_t storage_bytes,
+                             void *stream) {
+    int rc = check_gaussians(g);
+    if (rc) return rc;
+    if (!cfg || !cfg->alpha_threshold || !cfg->exp_power || !cfg->global_scale_factor) {
+        set_error("config scalars missing");
+        return EGR_EINVAL;
+    }
+    if (g->count == 0) return EGR_OK;
+    if (!storage || storage_bytes < bvh_layout(g->count).total) {
+        set_error("bvh storage too small: %zu < %zu", storage_bytes, bvh_layout(g->count).total);
+        return EGR_ENOMEM;
+    }
+    BvhView v = bvh_view(storage, g->count);
+    k_refit<<<(g->count + 255) / 256, 256, 0, (cudaStream_t)stream>>>(v, *g, *cfg);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}
+
+extern "C" int egr_bvh_build(const EgrGaussians *g, const EgrConfig *cfg, void *storage, size_t storage_bytes,
+                             void *scratch, size_t scratch_bytes, void *stream) {
+    int rc = check_gaussians(g);
+    if (rc) return rc;
+    const uint32_t n = g->count;
+    if (n == 0) return EGR_OK;
+    if (n > 0x3fffffffu) {
+        set_error("too many gaussians: %u", n);
+        return EGR_EINVAL;
+    }
+    BvhLayout L = bvh_layout(n);
+    BuildScratch B = build_scratch_layout(n);
+    if (!storage || storage_bytes < L.total) {
+        set_error("bvh storage too small: %zu < %zu", storage_bytes, L.total);
+        return EGR_ENOMEM;
+    }
+    if (!scratch || scratch_bytes < B.total) {
+        set_error("bvh scratch too small: %zu < %zu", scratch_bytes, B.total);
+        return EGR_ENOMEM;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    BvhView v = bvh_view(storage, n);
+    char *sb = (char *)scratch;
+    uint64_t *keys_in = (uint64_t *)(sb + B.keys_in), *keys_out = (uint64_t *)(sb + B.keys_out);
+    uint32_t *ids_in = (uint32_t *)(sb + B.ids_in);
+    uint32_t *child_l = (uint32_t *)(sb + B.child_l), *child_r = (uint32_t *)(sb + B.child_r);
+    uint32_t *parent_int = (uint32_t *)(sb + B.parent_int), *parent_leaf = (uint32_t *)(sb + B.parent_leaf);
+    uint32_t *first = (uint32_t *)(sb + B.first), *last = (uint32_t *)(sb + B.last);
+
+    k_bounds_init<<<1, 32, 0, st>>>(v.bounds);
+    int nb = (int)min((n + 255u) / 256u, 148u * 8u);
+    k_bounds<<<nb, 256, 0, st>>>(g->mean, n, v.bounds);
+    k_morton<<<(n + 255) / 256, 256, 0, st>>>(g->mean, n, v.bounds, keys_in, ids_in);
+    size_t cub_bytes = B.cub_bytes;
+    EGR_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sb + B.cub_temp, cub_bytes, keys_in, keys_out, ids_in, v.sorted_ids,
+                                                 (int)n, 0, 64, st));
+    if (n > 1) k_karras<<<(n - 1 + 255) / 256, 256, 0, st>>>(keys_out, (int)n, child_l, child_r, parent_int,
+                                                            parent_leaf, first, last);
+    k_preorder<<<(2 * n - 1 + 255) / 256, 256, 0, st>>>((int)n, child_l, parent_int, parent_leaf, first, last, v.nodes,
+                                                        v.parents, v.leaf_node, v.flags);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return egr_bvh_refit(g, cfg, storage, storage_bytes, stream);
+}
+
+extern "C" int egr_bvh_export(const void *storage, size_t storage_bytes, uint32_t n, uint32_t *sorted_ids,
+                              float *records, float *nodes, uint32_t *parents, void *stream) {
+    if (n == 0) return EGR_OK;
+    BvhLayout L = bvh_layout(n);
+    if (!storage || storage_bytes < L.total) {
+        set_error("bvh storage too small");
+        return EGR_ENOMEM;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    BvhView v = bvh_view(const_cast<void *>(storage), n);
+    if (sorted_ids) EGR_CUDA_TRY(cudaMemcpyAsync(sorted_ids, v.sorted_ids, (size_t)n * 4, cudaMemcpyDeviceToDevice, st));
+    if (records) EGR_CUDA_TRY(cudaMemcpyAsync(records, v.records, (size_t)n * 64, cudaMemcpyDeviceToDevice, st));
+    if (nodes) EGR_CUDA_TRY(cudaMemcpyAsync(nodes, v.nodes, (size_t)L.num_nodes * 32, cudaMemcpyDeviceToDevice, st));
+    if (parents) EGR_CUDA_TRY(cudaMemcpyAsync(parents, v.parents, (size_t)L.num_nodes * 4, cudaMemcpyDeviceToDevice, st));
+    return EGR_OK;
+}

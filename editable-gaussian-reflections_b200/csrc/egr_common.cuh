@@ -1,0 +1,254 @@
+// Shared device/host definitions of the B200-native Gaussian ray tracer (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/egr_b200.h"
+
+namespace egr {
+
+// ---- error plumbing (C ABI returns codes; message kept per thread) ------------------------------------
+void set_error(const char *fmt, ...);
+#define EGR_CUDA_TRY(expr)                                                                   \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            egr::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return EGR_ECUDA;                                                                \
+        }                                                                                    \
+    } while (0)
+
+// ---- constants of the reference's flags.h ---------------------------------------------------------------
+constexpr float A_MAX = 0.9999f;            // flags.h:8  MAX_ALPHA
+constexpr int KBUF = 16;                    // flags.h:16 BUFFER_SIZE
+constexpr int MAX_ITERATIONS = 99;          // flags.h:17
+constexpr float ROUGH_DOWNWEIGHT_POW = 3.f; // flags.h:12-13
+constexpr uint32_t INTERNAL = 0xFFFFFFFFu;  // node.leaf value of an internal node
+constexpr uint32_t NO_PARENT = 0xFFFFFFFFu;
+
+// ---- storage layouts -------------------------------------------------------------------------------------
+__host__ __device__ inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+// Persistent BVH storage.  Leaves are in Morton order ("leaf order"); records/appearance are permuted into it
+// so that spatially coherent rays touch contiguous sectors.  Nodes are 32 B, laid out in DFS preorder: the
+// left child of an internal node is node+1 and `skip` is the first node after the subtree, which makes the
+// traversal stackless (one index per warp).
+struct BvhLayout {
+    size_t sorted_ids, records, appearance, nodes, parents, leaf_node, flags, bounds, total;
+    uint32_t n, num_nodes;
+};
+__host__ __device__ inline BvhLayout bvh_layout(uint32_t n) {
+    BvhLayout L;
+    L.n = n;
+    L.num_nodes = n ? 2 * n - 1 : 0;
+    size_t o = 0;
+    L.bounds = o, o = align_up(o + 64, 256);
+    L.sorted_ids = o, o = align_up(o + (size_t)n * 4, 256);
+    L.records = o, o = align_up(o + (size_t)n * 64, 256);
+    L.appearance = o, o = align_up(o + (size_t)n * 48, 256);
+    L.nodes = o, o = align_up(o + (size_t)L.num_nodes * 32, 256);
+    L.parents = o, o = align_up(o + (size_t)L.num_nodes * 4, 256);
+    L.leaf_node = o, o = align_up(o + (size_t)n * 4, 256);
+    L.flags = o, o = align_up(o + (size_t)L.num_nodes * 4, 256);
+    L.total = o;
+    return L;
+}
+struct BvhView {
+    uint32_t n, num_nodes;
+    float *bounds;          // [6] scene bounds of the means (min xyz, max xyz) used for the Morton grid
+    uint32_t *sorted_ids;   // [n] leaf j -> Gaussian id
+    float4 *records;        // [n][4] geometry record in leaf order (layout: include/egr_b200.h)
+    float4 *appearance;     // [n][3] activated rgb,rough | normal,_ | f0,_
+    float4 *nodes;          // [num_nodes][2]: (bmin.xyz, skip) (bmax.xyz, leaf)
+    uint32_t *parents;      // [num_nodes] preorder index of the parent
+    uint32_t *leaf_node;    // [n] preorder index of leaf j
+    uint32_t *flags;        // [num_nodes] refit arrival counters (self-resetting)
+};
+inline BvhView bvh_view(void *storage, uint32_t n) {
+    BvhLayout L = bvh_layout(n);
+    char *b = (char *)storage;
+    BvhView v;
+    v.n = n, v.num_nodes = L.num_nodes;
+    v.bounds = (float *)(b + L.bounds);
+    v.sorted_ids = (uint32_t *)(b + L.sorted_ids);
+    v.records = (float4 *)(b + L.records);
+    v.appearance = (float4 *)(b + L.appearance);
+    v.nodes = (float4 *)(b + L.nodes);
+    v.parents = (uint32_t *)(b + L.parents);
+    v.leaf_node = (uint32_t *)(b + L.leaf_node);
+    v.flags = (uint32_t *)(b + L.flags);
+    return v;
+}
+
+// Per-pixel inter-step state: SoA float planes [S][P] (coalesced across the 32 pixels of a warp tile).
+enum StatePlane {
+    SP_RGB = 0,      // 3
+    SP_DEPTH = 3,
+    SP_NORMAL = 4,   // 3
+    SP_F0 = 7,       // 3
+    SP_ROUGH = 10,
+    SP_T = 11,
+    SP_TFULL = 12,
+    SP_REM_RGB = 13,   // 3
+    SP_REM_DEPTH = 16,
+    SP_REM_NORMAL = 17,  // 3
+    SP_REM_F0 = 20,      // 3
+    SP_REM_ROUGH = 23,
+    SP_THR = 24,     // 3 throughput after this step
+    SP_RAY_O = 27,   // 3 ray traced at this step
+    SP_RAY_D = 30,   // 3
+    SP_NEXT_O = 33,  // 3 ray spawned by this step (output_ray_origin/direction)
+    SP_NEXT_D = 36,  // 3
+    SP_NHITS = 39,   // int bits: composited hits of this step
+    SP_COUNT = 40
+};
+struct StateLayout {
+    size_t planes, steps_executed, warp_tail, total;
+    uint32_t P, S, num_warps;
+};
+__host__ __device__ inline uint32_t tiles_x(uint32_t w) { return (w + 7) / 8; }
+__host__ __device__ inline uint32_t tiles_y(uint32_t h) { return (h + 3) / 4; }
+__host__ __device__ inline StateLayout state_layout(uint32_t w, uint32_t h, uint32_t S) {
+    StateLayout L;
+    L.P = w * h, L.S = S;
+    L.num_warps = tiles_x(w) * tiles_y(h);
+    size_t o = 0;
+    L.planes = o, o = align_up(o + (size_t)SP_COUNT * S * L.P * 4, 256);
+    L.steps_executed = o, o = align_up(o + (size_t)L.P * 4, 256);
+    L.warp_tail = o, o = align_up(o + (size_t)L.num_warps * S * 8, 256);  // (tail chunk, num batches) per warp-step
+    L.total = o;
+    return L;
+}
+
+// Hit log: one 8 KiB chunk per (warp tile, batch of 16): slot-major [16][32] entries of 16 B
+// {leaf j, t, alpha, T_after} so that the 32 lanes write / read 512 contiguous bytes per slot, + a 128 B header
+// holding the previous chunk of the same warp-step.
+constexpr size_t HITLOG_CHUNK_BYTES = 128 + 16 * 32 * 16;
+
+// ---- small vector helpers -----------------------------------------------------------------------------------
+struct f3 {
+    float x, y, z;
+};
+__host__ __device__ inline f3 mk3(float x, float y, float z) { return f3{x, y, z}; }
+__host__ __device__ inline f3 operator+(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__host__ __device__ inline f3 operator-(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__host__ __device__ inline f3 operator*(f3 a, f3 b) { return mk3(a.x * b.x, a.y * b.y, a.z * b.z); }
+__host__ __device__ inline f3 operator*(f3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+__host__ __device__ inline f3 operator*(float s, f3 a) { return mk3(a.x * s, a.y * s, a.z * s); }
+__host__ __device__ inline f3 operator/(f3 a, f3 b) { return mk3(a.x / b.x, a.y / b.y, a.z / b.z); }
+__host__ __device__ inline f3 operator-(f3 a) { return mk3(-a.x, -a.y, -a.z); }
+__host__ __device__ inline f3 div_s(f3 a, float s) {
+    float inv = 1.0f / s;
+    return a * inv;
+}
+// canonical dot product of the hit-ID-critical path (mirrored by the oracle)
+__host__ __device__ inline float dot3(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+__host__ __device__ inline float dotp(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__host__ __device__ inline f3 cross3(f3 a, f3 b) {
+    return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__host__ __device__ inline f3 normalize3(f3 v) {
+    float inv = 1.0f / sqrtf(dotp(v, v));
+    return v * inv;
+}
+__host__ __device__ inline float length3(f3 v) { return sqrtf(dotp(v, v)); }
+__host__ __device__ inline float sign1(float v) { return copysignf(1.0f, v); }
+__host__ __device__ inline f3 sign3(f3 v) { return mk3(sign1(v.x), sign1(v.y), sign1(v.z)); }
+
+#ifdef __CUDACC__
+__device__ __forceinline__ f3 ld3(const float *p, size_t i) { return mk3(p[3 * i], p[3 * i + 1], p[3 * i + 2]); }
+__device__ __forceinline__ void st3(float *p, size_t i, f3 v) {
+    p[3 * i] = v.x, p[3 * i + 1] = v.y, p[3 * i + 2] = v.z;
+}
+
+// exp(u), u <= 0: Cody-Waite reduction + degree-7 Horner, IEEE-only sequence (bit-identical to the oracle's).
+__device__ __forceinline__ float det_exp(float u) {
+    if (!(u > -87.0f)) return 0.0f;
+    float n = rintf(u * 1.44269504088896341f);
+    float r = fmaf(-n, 0.693145751953125f, u);
+    r = fmaf(-n, 1.42860682030941723212e-6f, r);
+    float p = 1.0f / 5040.0f;
+    p = fmaf(p, r, 1.0f / 720.0f);
+    p = fmaf(p, r, 1.0f / 120.0f);
+    p = fmaf(p, r, 1.0f / 24.0f);
+    p = fmaf(p, r, 1.0f / 6.0f);
+    p = fmaf(p, r, 0.5f);
+    p = fmaf(p, r, 1.0f);
+    p = fmaf(p, r, 1.0f);
+    int e = (int)n;
+    return p * __int_as_float((e + 127) << 23);
+}
+__device__ __forceinline__ float det_pow(float d, float p) {
+    int ip = (int)p;
+    if ((float)ip == p && ip >= 1 && ip <= 8) {
+        float r = d;
+        for (int i = 1; i < ip; ++i) r = r * d;
+        return r;
+    }
+    return powf(d, p);
+}
+
+// RNG, integer exact (reference: csrc/utils/random.h:34-62)
+__device__ __forceinline__ uint32_t tea4(uint32_t v0, uint32_t v1) {
+    uint32_t s0 = 0;
+#pragma unroll
+    for (int n = 0; n < 4; ++n) {
+        s0 += 0x9e3779b9u;
+        v0 += ((v1 << 4) + 0xa341316cu) ^ (v1 + s0) ^ ((v1 >> 5) + 0xc8013ea4u);
+        v1 += ((v0 << 4) + 0xad90777du) ^ (v0 + s0) ^ ((v0 >> 5) + 0x7e95761eu);
+    }
+    return v0;
+}
+__device__ __forceinline__ float rnd01(uint32_t &prev) {
+    prev = 1664525u * prev + 1013904223u;
+    return (float)(prev & 0x00FFFFFFu) / (float)0x01000000;
+}
+
+// Result of evaluating one (ray, Gaussian) pair.
+struct HitEval {
+    float t, alpha, gaussval;
+    f3 x;   // local hit scaled by sf (reference: local_hit)
+    f3 dh;  // normalised object-space direction
+};
+// Reference: csrc/shaders.cu:9-75 (__intersection__gaussian).  `r0..r3` is the packed geometry record.
+// Returns false when rejected.  Every mul-add on this path is an explicit fmaf so that the oracle reproduces it
+// bit for bit.  The backface test (needs the normal) is done by the caller with `dh`.
+__device__ __forceinline__ bool eval_hit(
+    const float4 r0, const float4 r1, const float4 r2, const float4 r3, f3 o, f3 d, float tmin, float tmax,
+    float exp_power, HitEval &h) {
+    f3 w0 = mk3(r0.x, r0.y, r0.z), w1 = mk3(r1.x, r1.y, r1.z), w2 = mk3(r2.x, r2.y, r2.z);
+    f3 p = o - mk3(r0.w, r1.w, r2.w);
+    f3 ol = mk3(dot3(w0, p), dot3(w1, p), dot3(w2, p));
+    f3 dl = mk3(dot3(w0, d), dot3(w1, d), dot3(w2, d));
+    if (dot3(ol, dl) > 0.0f) return false;
+    float nn = sqrtf(dot3(dl, dl));
+    float inv = 1.0f / nn;
+    f3 dh = dl * inv;
+    float s = dot3(-ol, dh);
+    float t = s / nn;
+    f3 xu = mk3(fmaf(s, dh.x, ol.x), fmaf(s, dh.y, ol.y), fmaf(s, dh.z, ol.z));
+    if (dot3(xu, xu) > 1.0f) return false;
+    if (t < tmin || t > tmax) {  // segment-vs-unit-box test (OptiX AABB semantics), rarely needed
+        f3 idl = mk3(1.0f / dl.x, 1.0f / dl.y, 1.0f / dl.z);
+        float ax = (-1.0f - ol.x) * idl.x, bx = (1.0f - ol.x) * idl.x;
+        float ay = (-1.0f - ol.y) * idl.y, by = (1.0f - ol.y) * idl.y;
+        float az = (-1.0f - ol.z) * idl.z, bz = (1.0f - ol.z) * idl.z;
+        float tnear = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+        float tfar = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+        if (!(tfar >= tmin && tnear <= tmax)) return false;
+    }
+    float sf = r3.x, sigma = r3.y;
+    f3 x = xu * sf;
+    float d2 = dot3(x, x);
+    float g = det_exp(-det_pow(d2, exp_power) / (2.0f * exp_power));
+    h.t = t;
+    h.alpha = (A_MAX * g) * sigma;
+    h.gaussval = g;
+    h.x = x;
+    h.dh = dh;
+    return true;
+}
+#endif  // __CUDACC__
+
+}  // namespace egr

@@ -1,0 +1,533 @@
+// Forward tracer: one warp per 8x4 pixel tile walks the preorder LBVH as ONE warp-uniform node index (stackless,
+// warp-coherent), every lane testing its own ray; accepted hits update the exact total transmittance and a
+// 16-entry register k-buffer; batches of 16 are composited front to back exactly as the reference does
+// (window re-traversals replace its per-pixel linked-list re-walks), then the G-buffer of the step is finished
+// and the GGX bounce ray spawned.  One launch per step (wavefront) keeps the state between steps in HBM planes.
+//
+// Reference: editable_gauss_refl/cuda/csrc/shaders.cu:9-173, forward_pass.cu:3-156, core/camera.h:17-36,
+// core/framebuffer.h:104-143, utils/ggx_brdf.h:32-37,63,83,134-168, raytracer.cpp:81-94.
+#include <float.h>
+
+#include "egr_trace.cuh"
+
+namespace egr {
+
+int launch_pack_appearance(const BvhView &bvh, const EgrGaussians &g, cudaStream_t st);
+
+// ---- k-buffer: 16 (t, leaf) pairs sorted ascending by (t, leaf), in registers --------------------------------
+__device__ __forceinline__ bool kless(float t, uint32_t j, float t2, uint32_t j2) {
+    return t < t2 || (t == t2 && j < j2);
+}
+__device__ __forceinline__ void kb_reset(float (&kt)[KBUF], uint32_t (&kj)[KBUF]) {
+#pragma unroll
+    for (int i = 0; i < KBUF; ++i) kt[i] = FLT_MAX, kj[i] = 0xFFFFFFFFu;
+}
+// precondition: kless(t, j, kt[15], kj[15])
+__device__ __forceinline__ void kb_insert(float (&kt)[KBUF], uint32_t (&kj)[KBUF], float t, uint32_t j) {
+    bool lt[KBUF];
+#pragma unroll
+    for (int i = 0; i < KBUF; ++i) lt[i] = kless(t, j, kt[i], kj[i]);
+#pragma unroll
+    for (int i = KBUF - 1; i >= 1; --i) {
+        kt[i] = lt[i - 1] ? kt[i - 1] : (lt[i] ? t : kt[i]);
+        kj[i] = lt[i - 1] ? kj[i - 1] : (lt[i] ? j : kj[i]);
+    }
+    kt[0] = lt[0] ? t : kt[0];
+    kj[0] = lt[0] ? j : kj[0];
+}
+
+struct StepCfg {
+    float exp_power, bf_dist, bf_thr, tmin, tmax;
+    int step;
+};
+
+// Warp-uniform stackless walk.  PASS0 visits every node any lane's segment crosses (needed for the exact total
+// transmittance); later passes only the slab (w, kt[15]) of each lane.
+template <bool PASS0>
+__device__ __forceinline__ void traverse(
+    const BvhView &bvh, const StepCfg &sc, const f3 o, const f3 d, const f3 idir, const bool active, const float w,
+    float (&kt)[KBUF], uint32_t (&kj)[KBUF], float &T_full, int &n_acc, int &n_trav) {
+    const uint32_t end = bvh.num_nodes;
+    const float4 *__restrict__ nodes = bvh.nodes;
+    uint32_t node = 0;
+    while (node < end) {
+        const float4 A = __ldg(&nodes[2 * (size_t)node]);
+        const float4 B = __ldg(&nodes[2 * (size_t)node + 1]);
+        const uint32_t skip = __float_as_uint(A.w), leaf = __float_as_uint(B.w);
+        bool hit = false;
+        if (active && A.x <= B.x) {
+            float t0x = (A.x - o.x) * idir.x, t1x = (B.x - o.x) * idir.x;
+            float t0y = (A.y - o.y) * idir.y, t1y = (B.y - o.y) * idir.y;
+            float t0z = (A.z - o.z) * idir.z, t1z = (B.z - o.z) * idir.z;
+            float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
+            float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+            tn = tn - fabsf(tn) * 4.0e-7f;
+            tf = tf + fabsf(tf) * 4.0e-7f;
+            float lo = PASS0 ? sc.tmin : fmaxf(sc.tmin, w);
+            float hi = PASS0 ? sc.tmax : fminf(sc.tmax, kt[KBUF - 1]);
+            hit = fmaxf(tn, lo) <= fminf(tf, hi);
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, hit);
+        if (m == 0) {
+            node = skip;
+            continue;
+        }
+        if (leaf != INTERNAL) {
+            if (hit) {
+                const float4 r0 = __ldg(&bvh.records[4 * (size_t)leaf + 0]);
+                const float4 r1 = __ldg(&bvh.records[4 * (size_t)leaf + 1]);
+                const float4 r2 = __ldg(&bvh.records[4 * (size_t)leaf + 2]);
+                const float4 r3 = __ldg(&bvh.records[4 * (size_t)leaf + 3]);
+                n_trav++;
+                HitEval h;
+                bool ok = eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);
+                if (ok && sc.step != 0 && h.t < sc.bf_dist) {  // shaders.cu:53-61
+                    const float4 nq = __ldg(&bvh.appearance[3 * (size_t)leaf + 1]);
+                    f3 nrm = mk3(nq.x, nq.y, nq.z);
+                    if (sqrtf(dot3(nrm, nrm)) > sc.bf_thr && dot3(nrm, h.dh) > 0.0f) ok = false;
+                }
+                if (ok) {
+                    if (PASS0) {
+                        T_full = (float)((double)T_full * (1.0 - (double)h.alpha));  // shaders.cu:69-71
+                        n_acc++;
+                    }
+                    if (h.t > w && kless(h.t, leaf, kt[KBUF - 1], kj[KBUF - 1])) kb_insert(kt, kj, h.t, leaf);
+                }
+            }
+        }
+        node = node + 1;
+    }
+}
+
+// ---- per-call begin / end -----------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_begin(TraceCtx c, int grads) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i == 0) {
+        *c.p.metadata.grads_enabled = grads ? 1 : 0;  // metadata.h:28-31
+        *c.p.metadata.total_num_calls += 1;
+        c.p.stats.hitlog_status[0] = 0;  // chunks used by this call
+        c.p.stats.hitlog_status[1] = 0;  // overflow during this call ([2] is the sticky copy)
+    }
+    if (i < c.P) {  // stats.h:26-29
+        c.p.stats.num_accumulated_per_pixel[i] = 0;
+        c.p.stats.num_traversed_per_pixel[i] = 0;
+        c.p.stats.num_hits_per_pixel[i] = 0;
+        c.p.stats.num_composited_per_pixel[i] = 0;
+        c.p.stats.num_steps_per_pixel[i] = 0;
+        c.steps_executed[i] = 0;
+    }
+}
+__global__ void k_end(TraceCtx c) {  // raytracer.cpp:91-93 without the host sync
+    if (threadIdx.x == 0 && blockIdx.x == 0 && *c.p.config.accumulate_samples)
+        *c.p.framebuffer.accumulated_sample_count += 1;
+}
+
+// ---- one ray-step for every pixel ----------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int step, const int grads) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t lane = threadIdx.x & 31;
+    if (warp >= c.num_warps) return;
+    const EgrConfig &cfg = c.p.config;
+    const int B = min(*cfg.num_bounces, (int)c.S - 1);  // shaders.cu:85
+    if (step > B) return;
+    const uint32_t W = c.p.image_width, H = c.p.image_height;
+    const uint32_t px = (warp % c.tiles_x) * 8 + (lane & 7), py = (warp / c.tiles_x) * 4 + (lane >> 3);
+    const bool valid = px < W && py < H;
+    const uint32_t pix = valid ? py * W + px : 0;
+
+    bool alive;
+    f3 o, d;
+    uint32_t seed = 0;
+    if (step == 0) {
+        alive = valid;
+        seed = tea4(pix, *c.p.metadata.total_num_calls);  // shaders.cu:88
+        // camera.h:17-36
+        float view_size = tanf(*c.p.camera.vertical_fov_radians / 2);
+        float aspect = (float)W / (float)H;
+        float fx = (float)px, fy = (float)py;
+        if (*cfg.jitter_primary_rays) {
+            float jx = rnd01(seed) - 0.5f;
+            float jy = rnd01(seed) - 0.5f;
+            fx += jx, fy += jy;
+        }
+        float y = view_size * (1.0f - 2.0f * (fy + 1.0f / 2.0f) / (float)H);
+        float x = aspect * view_size * (2.0f * (fx + 1.0f / 2.0f) / (float)W - 1.0f);
+        const float *r = c.p.camera.rotation_w2c;
+        f3 w0 = mk3(r[0], r[1], r[2]), w1 = mk3(r[3], r[4], r[5]), w2 = mk3(r[6], r[7], r[8]);
+        o = mk3(c.p.camera.origin[0], c.p.camera.origin[1], c.p.camera.origin[2]);
+        d = normalize3(w0 * x + w1 * y - w2);
+    } else {
+        alive = valid && c.steps_executed[pix] == ((uint32_t)step | 0x100u);
+        if (alive) {
+            o = plane3(c, SP_NEXT_O, step - 1, pix);
+            d = plane3(c, SP_NEXT_D, step - 1, pix);
+            seed = c.p.metadata.random_seeds[pix];
+        } else {
+            o = mk3(0, 0, 0), d = mk3(0, 0, 1);
+        }
+    }
+    if (!__any_sync(0xffffffffu, alive)) return;
+
+    StepCfg sc;
+    sc.exp_power = *cfg.exp_power;
+    sc.bf_dist = *cfg.backfacing_max_dist;
+    sc.bf_thr = *cfg.backfacing_invalid_normal_threshold;
+    sc.tmin = step != 0 ? 0.0f : *c.p.camera.znear;  // forward_pass.cu:8-12
+    sc.tmax = *c.p.camera.zfar;
+    sc.step = step;
+    const float T_thr = *cfg.transmittance_threshold;
+    const f3 idir = mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+
+    float kt[KBUF];
+    uint32_t kj[KBUF];
+    float T_full = 1.0f, T = 1.0f;
+    int n_acc = 0, n_trav = 0, nh = 0;
+    f3 c_rgb = mk3(0, 0, 0), c_n = mk3(0, 0, 0), c_f0 = mk3(0, 0, 0);
+    float c_rough = 0.0f, c_depth = 0.0f;
+    float w = sc.tmin;
+    bool done = !alive;
+
+    kb_reset(kt, kj);
+    traverse<true>(c.bvh, sc, o, d, idir, alive, w, kt, kj, T_full, n_acc, n_trav);
+
+    uint32_t tail_chunk = 0xFFFFFFFFu, nbatches = 0;
+    bool log_ok = grads != 0;
+    char *hitlog = (char *)c.p.hitlog;
+
+    for (int it = 0;; ++it) {
+        if (!(w < sc.tmax) || kt[0] == FLT_MAX) done = true;  // forward_pass.cu:55,80-83
+        if (!__any_sync(0xffffffffu, !done)) break;
+        // one hit-log chunk per warp per batch (slot-major so that 32 lanes write 512 contiguous bytes)
+        float4 *chunk = nullptr;
+        if (grads) {
+            uint32_t cidx = 0;
+            if (lane == 0) cidx = log_ok ? atomicAdd(&c.p.stats.hitlog_status[0], 1u) : 0xFFFFFFFFu;
+            cidx = __shfl_sync(0xffffffffu, cidx, 0);
+            if (cidx >= c.hitlog_chunks) {
+                if (log_ok && lane == 0) c.p.stats.hitlog_status[1] = 1, c.p.stats.hitlog_status[2] = 1;  // overflow: this warp-step gets no backward
+                log_ok = false;
+            } else {
+                char *base = hitlog + (size_t)cidx * HITLOG_CHUNK_BYTES;
+                if (lane == 0) *(uint32_t *)base = tail_chunk;
+                chunk = (float4 *)(base + 128);
+                tail_chunk = cidx;
+                nbatches++;
+            }
+        }
+        if (!done) {
+#pragma unroll
+            for (int i = 0; i < KBUF; ++i) {
+                const float t = kt[i];
+                if (!done) {
+                    w = fmaxf(w, t);  // forward_pass.cu:89
+                    if (t < sc.tmax) {
+                        const uint32_t j = kj[i];
+                        const float4 r0 = __ldg(&c.bvh.records[4 * (size_t)j + 0]);
+                        const float4 r1 = __ldg(&c.bvh.records[4 * (size_t)j + 1]);
+                        const float4 r2 = __ldg(&c.bvh.records[4 * (size_t)j + 2]);
+                        const float4 r3 = __ldg(&c.bvh.records[4 * (size_t)j + 3]);
+                        HitEval h;
+                        eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);  // same bits as in the walk
+                        const float4 a0 = __ldg(&c.bvh.appearance[3 * (size_t)j + 0]);
+                        const float4 a1 = __ldg(&c.bvh.appearance[3 * (size_t)j + 1]);
+                        const float4 a2 = __ldg(&c.bvh.appearance[3 * (size_t)j + 2]);
+                        const float nextT = T * (1.0f - h.alpha);  // forward_pass.cu:108-115
+                        const float wt = T - nextT;
+                        c_rgb = c_rgb + mk3(a0.x, a0.y, a0.z) * wt;
+                        c_n = c_n + mk3(a1.x, a1.y, a1.z) * wt;
+                        c_f0 = c_f0 + mk3(a2.x, a2.y, a2.z) * wt;
+                        c_rough += a0.w * wt;
+                        c_depth += t * wt;
+                        T = nextT;
+                        if (chunk) chunk[i * 32 + lane] = make_float4(__uint_as_float(j), t, h.alpha, T);
+                        nh++;
+                        if (T < T_thr) {  // forward_pass.cu:131-134
+                            w = sc.tmax;
+                            done = true;
+                        }
+                    }
+                }
+            }
+        }
+        if (it + 1 >= MAX_ITERATIONS) done = true;
+        if (!(w < sc.tmax)) done = true;
+        if (!__any_sync(0xffffffffu, !done)) break;
+        kb_reset(kt, kj);
+        int dummy_acc = 0;
+        float dummy_T = 1.0f;
+        traverse<false>(c.bvh, sc, o, d, idir, !done, w, kt, kj, dummy_T, dummy_acc, n_trav);
+    }
+
+    if (lane == 0) {
+        uint32_t *wt_ = c.warp_tail + ((size_t)warp * c.S + step) * 2;
+        wt_[0] = log_ok ? tail_chunk : 0xFFFFFFFFu;
+        wt_[1] = log_ok ? nbatches : 0u;
+    }
+    if (!alive) return;
+
+    // ---- remaining fill (forward_pass.cu:143-155)
+    const float rem_T = T - T_full;
+    const float nrm = fmaxf(1.0f - T, *cfg.eps_forward_normalization);
+    f3 rem_rgb = div_s(c_rgb, nrm);
+    f3 o_rgb = c_rgb + rem_T * rem_rgb;
+    float rem_depth = c_depth / nrm;
+    float o_depth = c_depth + rem_T * rem_depth;
+    f3 rem_n = div_s(c_n, nrm);
+    f3 o_n = c_n + rem_T * rem_n;
+    f3 rem_f0 = div_s(c_f0, nrm);
+    f3 o_f0 = c_f0 + rem_T * rem_f0;
+    float rem_rough = c_rough / nrm;
+    float o_rough = c_rough + rem_T * rem_rough;
+
+    f3 thr_prev = mk3(1, 1, 1);
+    if (step > 0) {  // shaders.cu:112-114
+        thr_prev = plane3(c, SP_THR, step - 1, pix);
+        o_rgb = o_rgb * thr_prev;
+    }
+    set_plane3(c, SP_RGB, step, pix, o_rgb);
+    plane(c, SP_DEPTH, step, pix) = o_depth;
+    set_plane3(c, SP_NORMAL, step, pix, o_n);
+    set_plane3(c, SP_F0, step, pix, o_f0);
+    plane(c, SP_ROUGH, step, pix) = o_rough;
+    plane(c, SP_T, step, pix) = T;
+    plane(c, SP_TFULL, step, pix) = T_full;
+    if (grads) {
+        set_plane3(c, SP_REM_RGB, step, pix, rem_rgb);
+        plane(c, SP_REM_DEPTH, step, pix) = rem_depth;
+        set_plane3(c, SP_REM_NORMAL, step, pix, rem_n);
+        set_plane3(c, SP_REM_F0, step, pix, rem_f0);
+        plane(c, SP_REM_ROUGH, step, pix) = rem_rough;
+        set_plane3(c, SP_RAY_O, step, pix, o);
+        set_plane3(c, SP_RAY_D, step, pix, d);
+    }
+    plane(c, SP_NHITS, step, pix) = __int_as_float(log_ok || !grads ? nh : 0);
+    if (c.p.used_ray_origin) st3(c.p.used_ray_origin, (size_t)step * c.P + pix, o);
+    if (c.p.used_ray_direction) st3(c.p.used_ray_direction, (size_t)step * c.P + pix, d);
+    if (c.p.step_executed) c.p.step_executed[(size_t)step * c.P + pix] = 1;
+
+    c.p.stats.num_traversed_per_pixel[pix] += n_trav;
+    c.p.stats.num_hits_per_pixel[pix] += n_acc;
+    c.p.stats.num_composited_per_pixel[pix] += nh;
+    c.p.stats.num_steps_per_pixel[pix] += 1;
+    c.p.stats.num_accumulated_per_pixel[pix] = nh;  // forward_pass.cu:140 (last executed step wins)
+
+    // ---- bounce (shaders.cu:116-146)
+    uint32_t exec_code = (uint32_t)(step + 1);
+    f3 thr = mk3(1, 1, 1), next_o = mk3(0, 0, 0), next_d = mk3(0, 0, 0);
+    const f3 un = o_n;
+    if (!(length3(un) < *cfg.reflection_invalid_normal_threshold)) {
+        const f3 en = normalize3(un);
+        const float er = fmaxf(o_rough, *cfg.eps_min_roughness);
+        const f3 epos = o + o_depth * d;
+        const float u1 = rnd01(seed);
+        const float u2 = rnd01(seed);
+        const f3 V = -d;
+        // sample_cook_torrance (ggx_brdf.h:152-168)
+        const float a = er * er;
+        const float phi = (float)(2.0f * 3.14159265358979323846 * (double)u1);
+        const float cosT = sqrtf((1.0f - u2) / (1.0f + (a * a - 1.0f) * u2));
+        const float sinT = sqrtf(1.0f - cosT * cosT);
+        float sp, cp;
+        sincosf(phi, &sp, &cp);
+        const f3 Hl = mk3(sinT * cp, sinT * sp, cosT);
+        const f3 Tn = normalize3(cross3(en.z < 0.999f ? mk3(0, 0, 1) : mk3(1, 0, 0), en));
+        const f3 Bn = cross3(en, Tn);
+        const f3 Hh = Hl.x * Tn + Hl.y * Bn + Hl.z * en;
+        const f3 inc = -V;
+        next_d = inc - 2.0f * Hh * dotp(Hh, inc);
+        next_o = epos + *cfg.eps_ray_surface_offset * next_d;
+        // cook_torrance_weight (ggx_brdf.h:134-150)
+        f3 wgt = mk3(0, 0, 0);
+        if (!(o_f0.x == 0.0f && o_f0.y == 0.0f && o_f0.z == 0.0f)) {
+            const f3 L = next_d;
+            const f3 Hn = normalize3(V + L);
+            const float NdotH = fmaxf(dotp(en, Hn), 0.0f);
+            const float VdotH = fmaxf(dotp(V, Hn), 0.0f);
+            const float NdotV = fmaxf(dotp(en, V), 0.0f);
+            const float kk = (a * a) / 2.0f;
+            const float NdotL = fmaxf(dotp(en, L), 0.0f);
+            const float g1v = (float)(NdotV / ((double)(NdotV * (1.0f - kk) + kk) + 1e-8));
+            const float g1l = (float)(NdotL / ((double)(NdotL * (1.0f - kk) + kk) + 1e-8));
+            const float G = g1v * g1l;
+            const float pw = 1.0f - VdotH;
+            float p5 = pw * pw;
+            p5 = p5 * p5 * pw;
+            const f3 F = o_f0 + (mk3(1, 1, 1) - o_f0) * p5;
+            const float den = (float)((double)(NdotH * NdotV) + 1e-8);
+            wgt = div_s(F * G * VdotH, den);
+        }
+        thr = thr_prev * wgt;
+        exec_code |= 0x100u;
+    }
+    set_plane3(c, SP_THR, step, pix, thr);
+    set_plane3(c, SP_NEXT_O, step, pix, next_o);
+    set_plane3(c, SP_NEXT_D, step, pix, next_d);
+    c.steps_executed[pix] = exec_code;
+    c.p.metadata.random_seeds[pix] = seed;  // shaders.cu:172 (final value after the last executed step)
+}
+
+// ---- no-grad epilogue: accumulate + write every plane of every step (shaders.cu:163-169, framebuffer.h:104-143)
+__global__ void __launch_bounds__(256) k_resolve(const TraceCtx c) {
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix >= c.P) return;
+    const EgrFramebuffer &fb = c.p.framebuffer;
+    const int nexec = (int)(c.steps_executed[pix] & 0xFFu);
+    const bool accumulate = *c.p.config.accumulate_samples != 0;
+    const float dv = (float)(*fb.accumulated_sample_count + 1);
+    f3 fin = mk3(0, 0, 0);
+    for (int s = 0; s < (int)c.S; ++s) {
+        const bool ex = s < nexec;
+        f3 rgb = ex ? plane3(c, SP_RGB, s, pix) : mk3(0, 0, 0);
+        float depth = ex ? plane(c, SP_DEPTH, s, pix) : 0.0f;
+        f3 nrm = ex ? plane3(c, SP_NORMAL, s, pix) : mk3(0, 0, 0);
+        f3 f0 = ex ? plane3(c, SP_F0, s, pix) : mk3(0, 0, 0);
+        float rough = ex ? plane(c, SP_ROUGH, s, pix) : 0.0f;
+        float T = ex ? plane(c, SP_T, s, pix) : 1.0f;
+        float Tf = ex ? plane(c, SP_TFULL, s, pix) : 1.0f;
+        f3 no = ex ? plane3(c, SP_NEXT_O, s, pix) : mk3(0, 0, 0);
+        f3 nd = ex ? plane3(c, SP_NEXT_D, s, pix) : mk3(0, 0, 0);
+        const size_t q = (size_t)pix + (size_t)c.P * s;
+        if (accumulate) {
+            f3 a3 = ld3(fb.accumulated_rgb, q) + rgb;
+            st3(fb.accumulated_rgb, q, a3), rgb = div_s(a3, dv);
+            float a1 = fb.accumulated_transmittance[q] + T;
+            fb.accumulated_transmittance[q] = a1, T = a1 / dv;
+            a1 = fb.accumulated_total_transmittance[q] + Tf;
+            fb.accumulated_total_transmittance[q] = a1, Tf = a1 / dv;
+            a1 = fb.accumulated_depth[q] + depth;
+            fb.accumulated_depth[q] = a1, depth = a1 / dv;
+            a3 = ld3(fb.accumulated_normal, q) + nrm;
+            st3(fb.accumulated_normal, q, a3), nrm = div_s(a3, dv);
+            a3 = ld3(fb.accumulated_f0, q) + f0;
+            st3(fb.accumulated_f0, q, a3), f0 = div_s(a3, dv);
+            a1 = fb.accumulated_roughness[q] + rough;
+            fb.accumulated_roughness[q] = a1, rough = a1 / dv;
+        }
+        fin = fin + rgb;
+        st3(fb.output_rgb, q, rgb);
+        fb.output_depth[q] = depth;
+        st3(fb.output_normal, q, nrm);
+        st3(fb.output_f0, q, f0);
+        fb.output_roughness[q] = rough;
+        fb.output_transmittance[q] = T;
+        fb.output_total_transmittance[q] = Tf;
+        st3(fb.output_ray_origin, q, no);
+        st3(fb.output_ray_direction, q, nd);
+    }
+    st3(fb.output_final, pix, fin);
+}
+
+static int make_ctx(const EgrParams *p, TraceCtx &c) {
+    if (!p) {
+        set_error("params is null");
+        return EGR_EINVAL;
+    }
+    if (p->num_steps < 1 || p->num_steps > EGR_MAX_STEPS) {
+        set_error("num_steps %u out of range [1,%d]", p->num_steps, EGR_MAX_STEPS);
+        return EGR_EINVAL;
+    }
+    if (p->image_width == 0 || p->image_height == 0) {
+        set_error("empty image");
+        return EGR_EINVAL;
+    }
+    StateLayout L = state_layout(p->image_width, p->image_height, p->num_steps);
+    if (!p->pixel_state || p->pixel_state_bytes < L.total) {
+        set_error("pixel_state too small: %zu < %zu", p->pixel_state_bytes, L.total);
+        return EGR_ENOMEM;
+    }
+    if (p->gaussians.count && (!p->bvh_storage || p->bvh_storage_bytes < bvh_layout(p->gaussians.count).total)) {
+        set_error("bvh storage too small");
+        return EGR_ENOMEM;
+    }
+    c.p = *p;
+    c.bvh = bvh_view(p->bvh_storage, p->gaussians.count);
+    char *sb = (char *)p->pixel_state;
+    c.planes = (float *)(sb + L.planes);
+    c.steps_executed = (uint32_t *)(sb + L.steps_executed);
+    c.warp_tail = (uint32_t *)(sb + L.warp_tail);
+    c.P = L.P, c.S = L.S, c.tiles_x = tiles_x(p->image_width), c.num_warps = L.num_warps;
+    c.hitlog_chunks = p->hitlog ? (uint32_t)min((size_t)0x7fffffff, p->hitlog_bytes / HITLOG_CHUNK_BYTES) : 0;
+    return EGR_OK;
+}
+
+int launch_backward_impl(const TraceCtx &c, cudaStream_t st);
+int launch_hitlog_export(const TraceCtx &c, int step, int cap, int32_t *ids, float *ts, int32_t *counts, cudaStream_t st);
+
+}  // namespace egr
+
+using namespace egr;
+
+extern "C" size_t egr_pixel_state_bytes(uint32_t w, uint32_t h, uint32_t S) { return state_layout(w, h, S).total; }
+extern "C" size_t egr_hitlog_bytes_for_hits(uint64_t hits) {
+    // a chunk holds 16 hits for each of the 32 rays of a tile
+    return (size_t)((hits + 511) / 512) * HITLOG_CHUNK_BYTES;
+}
+
+extern "C" int egr_raytrace(const EgrParams *p, int grads_enabled, void *stream) {
+    TraceCtx c;
+    int rc = make_ctx(p, c);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (grads_enabled && !p->gaussians.grad_records) {
+        set_error("grads enabled but grad_records is null");
+        return EGR_EINVAL;
+    }
+    if (grads_enabled && c.hitlog_chunks == 0) {
+        set_error("grads enabled but no hit log was provided");
+        return EGR_EINVAL;
+    }
+    rc = launch_pack_appearance(c.bvh, p->gaussians, st);
+    if (rc) return rc;
+    k_begin<<<(c.P + 255) / 256, 256, 0, st>>>(c, grads_enabled);
+    const uint32_t blocks = (c.num_warps + 3) / 4;
+    for (uint32_t s = 0; s < c.S; ++s) k_trace_step<<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
+    if (grads_enabled) {
+        rc = launch_backward_impl(c, st);
+        if (rc) return rc;
+    } else {
+        k_resolve<<<(c.P + 255) / 256, 256, 0, st>>>(c);
+    }
+    k_end<<<1, 32, 0, st>>>(c);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}
+
+extern "C" int egr_hitlog_export(const EgrParams *p, int step, int cap, int32_t *ids, float *ts, int32_t *counts,
+                                 void *stream) {
+    TraceCtx c;
+    int rc = make_ctx(p, c);
+    if (rc) return rc;
+    if (step < 0 || step >= (int)c.S || cap < 0 || !ids || !counts || !p->hitlog) {
+        set_error("egr_hitlog_export: bad arguments");
+        return EGR_EINVAL;
+    }
+    return launch_hitlog_export(c, step, cap, ids, ts, counts, (cudaStream_t)stream);
+}
+
+extern "C" int egr_reset_accumulators(const EgrParams *p, void *stream) {
+    if (!p) {
+        set_error("params is null");
+        return EGR_EINVAL;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t SP = (size_t)p->num_steps * p->image_width * p->image_height;
+    const EgrFramebuffer &fb = p->framebuffer;
+    float *p3[3] = {fb.accumulated_rgb, fb.accumulated_normal, fb.accumulated_f0};
+    float *p1[4] = {fb.accumulated_transmittance, fb.accumulated_total_transmittance, fb.accumulated_depth,
+                    fb.accumulated_roughness};
+    for (float *q : p3) EGR_CUDA_TRY(cudaMemsetAsync(q, 0, SP * 12, st));
+    for (float *q : p1) EGR_CUDA_TRY(cudaMemsetAsync(q, 0, SP * 4, st));
+    EGR_CUDA_TRY(cudaMemsetAsync(fb.accumulated_sample_count, 0, 4, st));
+    return EGR_OK;
+}
+
+extern "C" int egr_denoise_passthrough(const EgrParams *p, void *stream) {
+    if (!p) {
+        set_error("params is null");
+        return EGR_EINVAL;
+    }
+    const size_t n = (size_t)p->image_width * p->image_height * 3;
+    EGR_CUDA_TRY(cudaMemcpyAsync(p->framebuffer.output_denoised, p->framebuffer.output_final, n * 4,
+                                 cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return EGR_OK;
+}

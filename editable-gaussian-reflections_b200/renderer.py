@@ -1,0 +1,130 @@
+"""Renderer facade: the caller side of the boundary, kept call-for-call identical to the reference's
+``editable_gauss_refl/renderer/gaussian_raytracer.py:10-151`` and ``gaussian_renderer.py:21-92`` so that
+``train.py`` / ``render.py`` / ``measure_fps.py`` / the viewer's edit->re-render sequence run unchanged against
+this binding.  ``pc`` is duck-typed (the attributes of ``GaussianModel`` the reference touches:
+``cfg, get_scaling, _get_scaling, _get_rotation, get_xyz, _opacity, get_diffuse, get_normal, get_roughness,
+get_f0`` and the raw ``_xyz ... _f0`` parameters with ``.grad``); ``camera`` needs ``R, FoVy, camera_center`` and
+the ``*_image`` targets.
+"""
+from __future__ import annotations
+
+import os
+from types import SimpleNamespace
+
+import numpy as np
+import torch
+
+
+class GaussianRaytracer:
+    def __init__(self, pc, image_width: int, image_height: int, **raytracer_kwargs):
+        from . import make_raytracer
+
+        self.image_width = image_width
+        self.image_height = image_height
+        self.cuda_module = make_raytracer(image_width, image_height, pc.get_scaling.shape[0], **raytracer_kwargs)
+        config = self.cuda_module.get_config()
+        config.loss_weight_diffuse.fill_(pc.cfg.loss_weight_diffuse)
+        config.loss_weight_specular.fill_(pc.cfg.loss_weight_specular)
+        config.loss_weight_normal.fill_(pc.cfg.loss_weight_normal)
+        config.loss_weight_depth.fill_(pc.cfg.loss_weight_depth)
+        config.loss_weight_f0.fill_(pc.cfg.loss_weight_f0)
+        config.loss_weight_roughness.fill_(pc.cfg.loss_weight_roughness)
+        config.transmittance_threshold.fill_(pc.cfg.transmittance_threshold)
+        config.alpha_threshold.fill_(pc.cfg.alpha_threshold)
+        config.exp_power.fill_(pc.cfg.exp_power)
+        self.pc = pc
+        self._export_param_values()
+        self.cuda_module.rebuild_bvh()
+
+    @torch.no_grad()
+    def rebuild_bvh(self):
+        self.cuda_module.resize(self.pc._xyz.shape[0])
+        self._export_param_values()
+        self.cuda_module.rebuild_bvh()
+
+    @torch.no_grad()
+    def _export_param_values(self):
+        g = self.cuda_module.get_gaussians()
+        g.scale.copy_(self.pc._get_scaling)
+        g.rotation.copy_(self.pc._get_rotation)
+        g.mean.copy_(self.pc.get_xyz)
+        g.opacity.copy_(self.pc._opacity)
+        g.rgb.copy_(self.pc.get_diffuse)
+        g.normal.copy_(self.pc.get_normal)
+        g.roughness.copy_(self.pc.get_roughness)
+        g.f0.copy_(self.pc.get_f0)
+
+    @torch.no_grad()
+    def _import_param_gradients(self):
+        g = self.cuda_module.get_gaussians()
+        self.pc._xyz.grad.add_(g.mean.grad)
+        self.pc._opacity.grad.add_(g.opacity.grad)
+        self.pc._scaling.grad.add_(g.scale.grad)
+        self.pc._rotation.grad.add_(g.rotation.grad)
+        self.pc._diffuse.grad.add_(g.rgb.grad)
+        self.pc._normal.grad.add_(g.normal.grad)
+        self.pc._roughness.grad.add_(g.roughness.grad)
+        self.pc._f0.grad.add_(g.f0.grad)
+
+    def zero_grad(self):
+        g = self.cuda_module.get_gaussians()
+        for name in ("rgb", "opacity", "scale", "rotation", "mean", "normal", "roughness", "f0"):
+            getattr(g, name).grad.zero_()
+
+    def __call__(self, viewpoint_camera, target=None, target_diffuse=None, target_specular=None, target_depth=None,
+                 target_normal=None, target_roughness=None, target_f0=None, force_update_bvh=False, denoise=False,
+                 znear=0.01, zfar=999.9):
+        with torch.no_grad():
+            R = viewpoint_camera.R
+            R = torch.from_numpy(R).cuda().float() if isinstance(R, np.ndarray) else R.cuda()
+            R_c2w_blender = -R
+            R_c2w_blender[:, 0] = -R_c2w_blender[:, 0]
+            camera = self.cuda_module.get_camera()
+            camera.znear.fill_(float(os.getenv("ZNEAR", znear)))
+            camera.zfar.fill_(float(os.getenv("ZFAR", zfar)))
+            camera.vertical_fov_radians.fill_(float(viewpoint_camera.FoVy))
+            camera.set_pose(viewpoint_camera.camera_center.contiguous(), R_c2w_blender.contiguous())
+            self._export_param_values()
+            fb = self.cuda_module.get_framebuffer()
+            for name, tgt in (("target_diffuse", target_diffuse), ("target_specular", target_specular),
+                              ("target_depth", target_depth), ("target_normal", target_normal),
+                              ("target_roughness", target_roughness), ("target_f0", target_f0)):
+                buf = getattr(fb, name)
+                if tgt is not None:
+                    buf.copy_(tgt.moveaxis(0, -1), non_blocking=True)
+                else:
+                    buf.zero_()
+        if torch.is_grad_enabled() or force_update_bvh:
+            self.cuda_module.update_bvh()
+        self.cuda_module.raytrace()
+        if denoise:
+            self.cuda_module.denoise()
+        if torch.is_grad_enabled():
+            self._import_param_gradients()
+        return {"render": fb.output_rgb.clone()}
+
+
+def render(camera, raytracer: GaussianRaytracer, targets_available=True, force_update_bvh=False, denoise=False,
+           znear=0.01, zfar=999.9):
+    do_backprop = torch.is_grad_enabled()
+    names = ("original_image", "diffuse_image", "specular_image", "normal_image", "f0_image", "roughness_image",
+             "depth_image")
+    if targets_available:
+        tgt, t_diff, t_spec, t_n, t_f0, t_r, t_d = (getattr(camera, n, None) for n in names)
+    else:
+        tgt = t_diff = t_spec = t_n = t_f0 = t_r = t_d = None
+    with torch.set_grad_enabled(do_backprop):
+        raytracer(camera, target=tgt, target_diffuse=t_diff, target_specular=t_spec, target_depth=t_d,
+                  target_normal=t_n, target_roughness=t_r, target_f0=t_f0, force_update_bvh=force_update_bvh,
+                  denoise=denoise, znear=znear, zfar=zfar)
+    fb = raytracer.cuda_module.get_framebuffer()
+
+    def chw(t):
+        return t.clone().detach().moveaxis(-1, 1)
+
+    rgb = chw(fb.output_rgb)
+    return SimpleNamespace(
+        rgb=rgb, final=chw(fb.output_denoised) if denoise else chw(fb.output_final), depth=chw(fb.output_depth),
+        normal=chw(fb.output_normal), roughness=chw(fb.output_roughness), f0=chw(fb.output_f0), target=tgt,
+        target_diffuse=t_diff, target_specular=t_spec, target_depth=t_d, target_normal=t_n, target_roughness=t_r,
+        target_f0=t_f0)

@@ -1,0 +1,187 @@
+/*
+ * egr_b200.h — C ABI of the B200-native differentiable Gaussian ray tracer.
+ *
+ * Drop-in boundary for the hot path of graphdeco-inria/editable-gaussian-reflections: everything the
+ * TorchScript class `raytracer.Raytracer` (reference: editable_gauss_refl/cuda/csrc/raytracer.cpp:24-218)
+ * does on the device is reachable through the entry points below.  Plain pointers and sizes only: no
+ * torch, no C++ types.  Every pointer is a DEVICE pointer owned by the caller unless stated otherwise; the
+ * library allocates nothing (all storage / scratch is sized by the *_bytes() queries and passed in), never
+ * synchronises the host, and enqueues all work on the stream handed in (`void*` = cudaStream_t).
+ *
+ * Every function returns 0 on success or a negative EGR_E* code; egr_last_error() returns the message of the
+ * last failure on the calling thread (the Python shim raises RuntimeError from it, preserving the reference's
+ * exception convention, csrc/utils/exception.h:48-78).
+ *
+ * The structs mirror the reference's raw-pointer device structs one to one:
+ *   EgrCamera      <- struct Camera       csrc/core/camera.h:8-15
+ *   EgrConfig      <- struct Config       csrc/core/config.h:5-26
+ *   EgrFramebuffer <- struct Framebuffer  csrc/core/framebuffer.h:72-102
+ *   EgrGaussians   <- struct Gaussians    csrc/core/gaussians.h:3-25
+ *   EgrMetadata    <- struct Metadata     csrc/core/metadata.h:3-7
+ *   EgrStats       <- struct Stats        csrc/core/stats.h:3-6
+ *   EgrParams      <- struct Params       csrc/params.h:11-26
+ */
+#ifndef EGR_B200_H
+#define EGR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define EGR_ABI_VERSION 1
+#define EGR_MAX_STEPS 8          /* upper bound on MAX_BOUNCES+1 (reference: flags.h:5 fixes MAX_BOUNCES=2) */
+#define EGR_GRAD_STRIDE 24       /* floats per Gaussian in the flat gradient record, see EgrGaussians */
+#define EGR_RECORD_FLOATS 16     /* floats per packed geometry record */
+
+#define EGR_OK 0
+#define EGR_EINVAL (-1)          /* bad argument (null pointer, size mismatch, too many steps ...) */
+#define EGR_ENOMEM (-2)          /* a caller-provided buffer is smaller than the matching *_bytes() query */
+#define EGR_ECUDA (-3)           /* a CUDA call failed; message holds cudaGetErrorString */
+
+typedef struct EgrCamera {       /* csrc/core/camera.h:8-15 */
+    const float *origin;                 /* [3]   */
+    const float *vertical_fov_radians;   /* [1]   */
+    const float *rotation_c2w;           /* [3,3] row-major */
+    const float *rotation_w2c;           /* [3,3] row-major (= transpose) */
+    const float *znear;                  /* [1]   */
+    const float *zfar;                   /* [1]   */
+} EgrCamera;
+
+typedef struct EgrConfig {       /* csrc/core/config.h:5-26; one-element device scalars, read on the device */
+    const float *exp_power;
+    const float *alpha_threshold;
+    const float *transmittance_threshold;
+    const uint8_t *accumulate_samples;   /* bool */
+    const uint8_t *jitter_primary_rays;  /* bool */
+    const int32_t *num_bounces;
+    const float *global_scale_factor;
+    const float *loss_weight_diffuse;
+    const float *loss_weight_specular;
+    const float *loss_weight_depth;
+    const float *loss_weight_normal;
+    const float *loss_weight_f0;
+    const float *loss_weight_roughness;
+    const float *eps_forward_normalization;
+    const float *eps_scale_grad;
+    const float *eps_ray_surface_offset;
+    const float *eps_min_roughness;
+    const float *reflection_invalid_normal_threshold;
+    const float *backfacing_invalid_normal_threshold;
+    const float *backfacing_max_dist;
+} EgrConfig;
+
+typedef struct EgrFramebuffer {  /* csrc/core/framebuffer.h:72-102; planes are [S,H,W,C], step-major */
+    float *output_rgb, *output_depth, *output_normal, *output_f0, *output_roughness, *output_transmittance,
+        *output_total_transmittance, *output_ray_origin, *output_ray_direction;
+    float *output_final, *output_denoised;          /* [1,H,W,3] */
+    float *accumulated_rgb, *accumulated_transmittance, *accumulated_total_transmittance, *accumulated_depth,
+        *accumulated_normal, *accumulated_f0, *accumulated_roughness;
+    int32_t *accumulated_sample_count;              /* [1] */
+    const float *target_diffuse, *target_specular, *target_depth, *target_normal, *target_f0,
+        *target_roughness;                          /* [H,W,C] */
+} EgrFramebuffer;
+
+typedef struct EgrGaussians {    /* csrc/core/gaussians.h:3-25; raw (pre-activation) parameters */
+    uint32_t count;
+    const float *rgb, *normal, *f0;      /* [N,3] */
+    const float *roughness, *opacity;    /* [N,1] */
+    const float *scale, *mean;           /* [N,3] */
+    const float *rotation;               /* [N,4] (r,x,y,z) */
+    /* The reference's eight dL_d* arrays + total_weight are ONE flat [N, EGR_GRAD_STRIDE] fp32 record here so
+     * that a hit is flushed with 128-bit vector reductions and a multi-GPU job all-reduces one buffer:
+     *   0-2 dL_dmean   3 dL_dopacity | 4-6 dL_dscale  7 dL_droughness | 8-11 dL_drotation |
+     *   12-14 dL_drgb 15 total_weight | 16-18 dL_dnormal 19 pad | 20-22 dL_df0 23 pad
+     * (the Python binding exposes the reference's tensors as strided views of it).  16-byte aligned. */
+    float *grad_records;
+} EgrGaussians;
+
+typedef struct EgrMetadata {     /* csrc/core/metadata.h:3-7 */
+    uint8_t *grads_enabled;      /* [1] bool, written by egr_raytrace */
+    uint32_t *total_num_calls;   /* [1], incremented by egr_raytrace before tracing (metadata.h:28-31) */
+    uint32_t *random_seeds;      /* [H,W,1] */
+} EgrMetadata;
+
+typedef struct EgrStats {        /* csrc/core/stats.h:3-6 + three extra planes used by the roofline formula */
+    int32_t *num_accumulated_per_pixel;  /* [H,W] composited hits of the last executed step */
+    int32_t *num_traversed_per_pixel;    /* [H,W] candidates tested (implementation-defined, as in OptiX) */
+    int32_t *num_hits_per_pixel;         /* [H,W] accepted hits, summed over steps */
+    int32_t *num_composited_per_pixel;   /* [H,W] composited hits, summed over steps */
+    int32_t *num_steps_per_pixel;        /* [H,W] executed ray-steps */
+    uint32_t *hitlog_status;             /* [4]: chunks used, overflow flag, reserved, reserved */
+} EgrStats;
+
+typedef struct EgrParams {       /* csrc/params.h:11-26 */
+    uint32_t image_width, image_height;
+    uint32_t num_steps;          /* S = MAX_BOUNCES+1 the planes were allocated with (<= EGR_MAX_STEPS) */
+    uint32_t reserved0;
+    EgrCamera camera;
+    EgrConfig config;
+    EgrFramebuffer framebuffer;
+    EgrGaussians gaussians;
+    EgrMetadata metadata;
+    EgrStats stats;
+    void *bvh_storage;           /* built by egr_bvh_build, sized by egr_bvh_storage_bytes(count) */
+    size_t bvh_storage_bytes;
+    void *pixel_state;           /* inter-step per-pixel state, sized by egr_pixel_state_bytes */
+    size_t pixel_state_bytes;
+    void *hitlog;                /* composited-hit log read by the backward; may be NULL when grads are off */
+    size_t hitlog_bytes;
+    /* debug planes, may be NULL: the ray traced at each step and whether the step ran ([S,H,W,3] / [S,H,W]) */
+    float *used_ray_origin, *used_ray_direction;
+    int32_t *step_executed;
+} EgrParams;
+
+/* ---- library ------------------------------------------------------------------------------------------ */
+int egr_abi_version(void);
+const char *egr_last_error(void);
+
+/* Compile-time constants the reference exports as static methods (csrc/raytracer.cpp:145-148, flags.h). */
+double egr_max_alpha(void);
+int egr_roughness_downweight_grad(void);
+double egr_roughness_downweight_grad_power(void);
+int egr_buffer_size(void);      /* flags.h:16 */
+int egr_max_iterations(void);   /* flags.h:17 */
+
+/* ---- BVH (replaces csrc/optix/bvh_wrapper.{h,cu}) ------------------------------------------------------ */
+size_t egr_bvh_storage_bytes(uint32_t num_gaussians);
+size_t egr_bvh_scratch_bytes(uint32_t num_gaussians);
+/* Full build: Morton codes of the means, radix sort, Karras topology, preorder layout, then a refit.
+ * Replaces BVHWrapper::rebuild / build_tlas (bvh_wrapper.h:24-30,118-157). */
+int egr_bvh_build(const EgrGaussians *g, const EgrConfig *cfg, void *storage, size_t storage_bytes, void *scratch,
+                  size_t scratch_bytes, void *stream);
+/* Refit: re-pack the geometry records from the current parameters and refresh all boxes bottom-up.
+ * Replaces BVHWrapper::update = populateBVH + optixAccelBuild(UPDATE) (bvh_wrapper.h:32-59,
+ * bvh_wrapper.cu:33-70) without its three host syncs. */
+int egr_bvh_refit(const EgrGaussians *g, const EgrConfig *cfg, void *storage, size_t storage_bytes, void *stream);
+
+/* ---- tracer (replaces Raytracer::raytrace, csrc/raytracer.cpp:81-94, and the OptiX launch of
+ *      __raygen__rg / __intersection__gaussian, csrc/shaders.cu:9-173) -------------------------------- */
+size_t egr_pixel_state_bytes(uint32_t width, uint32_t height, uint32_t num_steps);
+size_t egr_hitlog_bytes_for_hits(uint64_t num_hits_capacity);
+/* One raytrace() call: metadata update, stats reset, forward for all steps and then either the fused-loss
+ * backward (grads_enabled != 0; nothing is written to the framebuffer, shaders.cu:155-169) or accumulation +
+ * output writes, and the accumulated_sample_count bump. */
+int egr_raytrace(const EgrParams *p, int grads_enabled, void *stream);
+
+/* FramebufferDataHolder::reset_accumulators (csrc/core/framebuffer.h:249-258) as one launch. */
+int egr_reset_accumulators(const EgrParams *p, void *stream);
+/* DenoiserWrapper::run (csrc/optix/denoiser_wrapper.h:76-104): the OptiX AI denoiser is a proprietary
+ * driver-resident network, unavailable here; this is the documented pass-through output_final -> output_denoised. */
+int egr_denoise_passthrough(const EgrParams *p, void *stream);
+
+/* Debug/test access: copies of internal arrays (device to device, on `stream`). */
+int egr_bvh_export(const void *storage, size_t storage_bytes, uint32_t num_gaussians, uint32_t *sorted_ids,
+                   float *records, float *nodes, uint32_t *parents, void *stream);
+
+/* Decode the hit log of the last grads-enabled egr_raytrace: per pixel, the ORIGINAL Gaussian ids (and distances)
+ * of the hits composited at `step`, in composite order; ids/ts are [H*W, cap], counts [H*W] (not capped).
+ * Plays the role of walking the reference's backward per-pixel linked list (per_pixel_linked_list.h:19-75). */
+int egr_hitlog_export(const EgrParams *p, int step, int cap, int32_t *ids, float *ts, int32_t *counts, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* EGR_B200_H */

@@ -1,0 +1,774 @@
+// =============================================================================================
+// ORACLE — TEST INFRASTRUCTURE ONLY.  Not part of the product; nothing under the product package
+// may import, link or execute this file.  Only tests/, __graft_entry__.smoke() and the
+// cpu_baseline / --impl reference legs of bench.py use it, and only as the checker.
+//
+// CPU restatement (C++17 + OpenMP, brute force over Gaussians, no BVH) of the differentiable
+// Gaussian ray tracer of graphdeco-inria/editable-gaussian-reflections.  Citations are relative
+// to /root/reference/editable_gauss_refl/cuda/csrc/ :
+//   shaders.cu:9-75       per-candidate accept/reject, response, exact total transmittance
+//   shaders.cu:77-173     step loop, bounce spawn, throughput, final, grad/no-grad outputs
+//   forward_pass.cu:3-156 16-wide batch selection with strict window, compositing, remaining fill
+//   backward_pass.cu:3-222 in-kernel L1 gradients, back-to-front suffix sums, geometry gradients
+//   utils/kernel.cu:3-16, utils/activations.cu, utils/helpers.cu:10-58, utils/misc.cu:56-63
+//   utils/random.h:34-62 (tea<4>, lcg, rnd), utils/ggx_brdf.h:32-37,63,83,134-168
+//   core/camera.h:17-36, optix/bvh_wrapper.cu:9-59, core/framebuffer.h:104-152
+//
+// Parity status: the reference's own tests hold no golden vector for this path (its tracer is
+// GPU/OptiX only).  This restatement is pinned instead against the reference's literal shader
+// sources compiled as host C++ (oracle/ref_shim -> oracle/_ref, see oracle/README.md) and the
+// fixtures under tests/golden/ record that agreement.
+//
+// Arithmetic conventions (documented in DESIGN.md, mirrored by the CUDA kernels so that hit-ID
+// lists can be compared bit-exactly):
+//   * dot3(a,b) = fmaf(a.z,b.z, fmaf(a.y,b.y, a.x*b.x)) on the accept/reject + distance path;
+//   * exp() of the Gaussian response is evaluated by det_exp() (Cody-Waite + degree-7 Horner,
+//     <= 2 ulp), integer exp_power by repeated multiplication; both are IEEE-only sequences and
+//     therefore bit-identical on CPU and GPU;
+//   * candidate enumeration = every visible Gaussian whose local unit box [-1,1]^3 is crossed by
+//     the ray segment [tmin,tmax] (OptiX AABB semantics), tested explicitly.
+// Build: g++ -O2 -fopenmp -ffp-contract=off -shared -fPIC (see oracle/Makefile).
+// =============================================================================================
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <limits>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+namespace {
+
+struct f3 {
+    float x, y, z;
+};
+inline f3 mk(float x, float y, float z) { return f3{x, y, z}; }
+inline f3 operator+(f3 a, f3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+inline f3 operator-(f3 a, f3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+inline f3 operator*(f3 a, f3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+inline f3 operator*(f3 a, float s) { return mk(a.x * s, a.y * s, a.z * s); }
+inline f3 operator*(float s, f3 a) { return mk(a.x * s, a.y * s, a.z * s); }
+inline f3 operator/(f3 a, f3 b) { return mk(a.x / b.x, a.y / b.y, a.z / b.z); }
+inline f3 div_s(f3 a, float s) {  // vec_math.h:330-333: float3 / float multiplies by the reciprocal
+    float inv = 1.0f / s;
+    return a * inv;
+}
+inline f3 operator-(f3 a) { return mk(-a.x, -a.y, -a.z); }
+// canonical dot product of the ID-critical path
+inline float dot3(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+// plain dot product (vec_math.h:365 order) for the non-critical shading / gradient code
+inline float dotp(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline f3 cross(f3 a, f3 b) { return mk(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
+inline float length(f3 a) { return sqrtf(dotp(a, a)); }
+inline f3 normalize(f3 v) {  // vec_math.h:376-379
+    float inv = 1.0f / sqrtf(dotp(v, v));
+    return v * inv;
+}
+inline f3 ld3(const float *p, size_t i) { return mk(p[3 * i], p[3 * i + 1], p[3 * i + 2]); }
+inline void st3(float *p, size_t i, f3 v) {
+    p[3 * i] = v.x;
+    p[3 * i + 1] = v.y;
+    p[3 * i + 2] = v.z;
+}
+inline float sign1(float v) { return copysignf(1.0f, v); }  // misc.cu:56-63 (sign(0)=+1, sign(-0)=-1)
+inline f3 sign3(f3 v) { return mk(sign1(v.x), sign1(v.y), sign1(v.z)); }
+
+constexpr float A_MAX = 0.9999f;        // flags.h:8
+constexpr int BUFFER_SIZE = 16;         // flags.h:16
+constexpr int MAX_ITERATIONS = 99;      // flags.h:17
+constexpr float ROUGH_DOWNWEIGHT_POW = 3.0f;  // flags.h:12-13
+
+// ---- deterministic exp (shared definition with the CUDA kernels) ---------------------------
+inline float det_exp(float u) {
+    if (!(u > -87.0f)) return 0.0f;
+    float n = rintf(u * 1.44269504088896341f);
+    float r = fmaf(-n, 0.693145751953125f, u);          // ln2 hi (exact in 12 bits)
+    r = fmaf(-n, 1.42860682030941723212e-6f, r);        // ln2 lo
+    float p = 1.0f / 5040.0f;
+    p = fmaf(p, r, 1.0f / 720.0f);
+    p = fmaf(p, r, 1.0f / 120.0f);
+    p = fmaf(p, r, 1.0f / 24.0f);
+    p = fmaf(p, r, 1.0f / 6.0f);
+    p = fmaf(p, r, 0.5f);
+    p = fmaf(p, r, 1.0f);
+    p = fmaf(p, r, 1.0f);
+    int e = (int)n;
+    uint32_t bits = (uint32_t)(e + 127) << 23;
+    float s;
+    std::memcpy(&s, &bits, 4);
+    return p * s;
+}
+// d^p: integer p in [1,8] by left-to-right repeated multiplication, else powf
+inline float det_pow(float d, float p) {
+    int ip = (int)p;
+    if ((float)ip == p && ip >= 1 && ip <= 8) {
+        float r = d;
+        for (int i = 1; i < ip; ++i) r = r * d;
+        return r;
+    }
+    return powf(d, p);
+}
+
+// ---- RNG (utils/random.h:34-62) -----------------------------------------------------------
+inline uint32_t tea4(uint32_t v0, uint32_t v1) {
+    uint32_t s0 = 0;
+    for (int n = 0; n < 4; ++n) {
+        s0 += 0x9e3779b9u;
+        v0 += ((v1 << 4) + 0xa341316cu) ^ (v1 + s0) ^ ((v1 >> 5) + 0xc8013ea4u);
+        v1 += ((v0 << 4) + 0xad90777du) ^ (v0 + s0) ^ ((v0 >> 5) + 0x7e95761eu);
+    }
+    return v0;
+}
+inline float rnd(uint32_t &prev) {
+    prev = 1664525u * prev + 1013904223u;
+    return (float)(prev & 0x00FFFFFFu) / (float)0x01000000;
+}
+
+}  // namespace
+
+extern "C" {
+
+struct OrcConfig {
+    float exp_power, alpha_threshold, transmittance_threshold, global_scale_factor;
+    float loss_weight_diffuse, loss_weight_specular, loss_weight_depth, loss_weight_normal, loss_weight_f0,
+        loss_weight_roughness;
+    float eps_forward_normalization, eps_scale_grad, eps_ray_surface_offset, eps_min_roughness;
+    float reflection_invalid_normal_threshold, backfacing_invalid_normal_threshold, backfacing_max_dist;
+    int32_t num_bounces, jitter_primary_rays, accumulate_samples, max_bounces;
+};
+struct OrcCamera {
+    float origin[3];
+    float rot_c2w[9];  // row-major; rotation_w2c is its transpose (camera.h:62-68)
+    float fovy, znear, zfar;
+};
+struct OrcScene {
+    int32_t n;
+    const float *mean, *scale, *rotation, *opacity, *rgb, *normal, *f0, *roughness;  // raw (pre-activation)
+};
+struct OrcTargets {  // [P,C]; may be all-null when grads are off
+    const float *diffuse, *specular, *depth, *normal, *f0, *roughness;
+};
+struct OrcOutputs {  // [S,P,C] step-major planes (framebuffer.h:108,132); any pointer may be null
+    float *rgb, *depth, *normal, *f0, *roughness, *transmittance, *total_transmittance, *ray_origin, *ray_direction;
+    float *final_;  // [P,3]
+    float *acc_rgb, *acc_transmittance, *acc_total_transmittance, *acc_depth, *acc_normal, *acc_f0, *acc_roughness;
+    int32_t *acc_count;  // [1], read only here (the host bumps it after the launch, raytracer.cpp:91-93)
+    uint32_t *random_seeds;           // [P]
+    int32_t *num_accumulated;         // [P] composited hits of the LAST executed forward_pass (forward_pass.cu:140)
+    int32_t *num_hits_per_pixel;      // [P] accepted hits summed over steps
+    int32_t *num_composited_per_pixel;  // [P] composited hits summed over steps
+    int32_t *num_steps_per_pixel;     // [P] executed ray-steps
+    float *used_ray_origin, *used_ray_direction;  // [S,P,3] the ray traced at each step
+    int32_t *step_executed;           // [S,P]
+};
+struct OrcGrads {  // accumulated INTO (+=); any pointer may be null only if grads are off
+    float *dL_drgb, *dL_dnormal, *dL_df0, *dL_droughness, *dL_dopacity, *dL_dscale, *dL_dmean, *dL_drotation;
+    float *total_weight;
+};
+struct OrcHitLists {  // optional (cap = 0 disables)
+    int32_t cap;
+    int32_t *counts;  // [S,P] composited count (not capped)
+    int32_t *ids;     // [S,P,cap]
+    float *ts;        // [S,P,cap]
+};
+struct OrcOverride {  // optional: trace these rays instead of the oracle's own (bit-exact ID tests)
+    const float *ray_origin, *ray_direction;  // [S,P,3]
+    const int32_t *step_executed;             // [S,P]
+    const float *records;                     // [N,16] packed geometry records, layout of orc_prepare
+};
+
+int orc_num_threads() {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+
+// Record layout (16 floats): W row0 xyz, mean.x | W row1 xyz, mean.y | W row2 xyz, mean.z | sf, sigma, id-bits, visible
+// bvh_wrapper.cu:9-59 (transform, visibility), kernel.cu:3-6 (scaling factor), activations.cu:5,59,67-69
+void orc_prepare(const OrcScene *sc, const OrcConfig *cfg, float *rec) {
+    const float k = 2.0f * cfg->exp_power;
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < sc->n; ++i) {
+        float sigma = 1.0f / (1.0f + expf(-sc->opacity[i]));
+        float sf = sigma <= cfg->alpha_threshold ? 0.0f : powf(k * logf(sigma / cfg->alpha_threshold), 1.0f / k);
+        f3 s = mk(expf(sc->scale[3 * i]), expf(sc->scale[3 * i + 1]), expf(sc->scale[3 * i + 2]));
+        f3 S = s * sf * cfg->global_scale_factor;
+        float r = sc->rotation[4 * i], x = sc->rotation[4 * i + 1], y = sc->rotation[4 * i + 2],
+              z = sc->rotation[4 * i + 3];
+        float norm = sqrtf(r * r + x * x + y * y + z * z);
+        r /= norm, x /= norm, y /= norm, z /= norm;
+        float R[3][3] = {
+            {1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+            {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+            {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+        // The reference marks an instance visible iff sf > 0 and any size > 0; with all sizes required > 0 the
+        // analytic inverse W = diag(1/S) R^T exists (a zero size is a degenerate transform OptiX cannot invert).
+        bool visible = sf > 0.0f && S.x > 0.0f && S.y > 0.0f && S.z > 0.0f && std::isfinite(norm) && norm > 0.0f;
+        float Sv[3] = {S.x, S.y, S.z};
+        float *o = rec + 16 * (size_t)i;
+        for (int rr = 0; rr < 3; ++rr) {
+            for (int c = 0; c < 3; ++c) o[4 * rr + c] = visible ? R[c][rr] / Sv[rr] : 0.0f;
+            o[4 * rr + 3] = sc->mean[3 * i + rr];
+        }
+        o[12] = sf;
+        o[13] = sigma;
+        uint32_t id = (uint32_t)i;
+        std::memcpy(&o[14], &id, 4);
+        o[15] = visible ? 1.0f : 0.0f;
+    }
+}
+
+}  // extern "C"
+
+namespace {
+
+struct Hit {
+    float t;
+    int32_t id;
+    float alpha, gaussval;
+    f3 x;  // local hit (scaled by sf)
+};
+
+struct RayResult {
+    float T_full;
+    int n_accepted;
+    std::vector<Hit> hits;  // all accepted hits, sorted by (t, id)
+};
+
+// shaders.cu:9-75 for one (ray, Gaussian) pair given the packed record.  Returns true when accepted.
+inline bool candidate(
+    const float *rec, const float *normals, const OrcConfig &cfg, int step, f3 o, f3 d, float tmin, float tmax, Hit &h) {
+    if (rec[15] == 0.0f) return false;
+    f3 w0 = mk(rec[0], rec[1], rec[2]), w1 = mk(rec[4], rec[5], rec[6]), w2 = mk(rec[8], rec[9], rec[10]);
+    f3 mu = mk(rec[3], rec[7], rec[11]);
+    f3 p = o - mu;
+    f3 ol = mk(dot3(w0, p), dot3(w1, p), dot3(w2, p));
+    f3 dl = mk(dot3(w0, d), dot3(w1, d), dot3(w2, d));
+    if (dot3(ol, dl) > 0.0f) return false;  // shaders.cu:36
+    float nn = sqrtf(dot3(dl, dl));          // shaders.cu:41
+    float inv = 1.0f / nn;                   // vec_math.h:337-340
+    f3 dh = dl * inv;
+    float s = dot3(-ol, dh);                 // shaders.cu:43
+    float t = s / nn;                        // shaders.cu:44
+    f3 xu = mk(fmaf(s, dh.x, ol.x), fmaf(s, dh.y, ol.y), fmaf(s, dh.z, ol.z));  // shaders.cu:45
+    if (dot3(xu, xu) > 1.0f) return false;   // shaders.cu:48-51
+    // OptiX presents only instances whose unit box is crossed by the segment [tmin,tmax]
+    // (forward_pass.cu:24-43).  The closest-approach point lies inside the box, so the slab test is
+    // only needed when t itself is outside the segment.
+    if (t < tmin || t > tmax) {
+        f3 idl = mk(1.0f / dl.x, 1.0f / dl.y, 1.0f / dl.z);
+        float ax = (-1.0f - ol.x) * idl.x, bx = (1.0f - ol.x) * idl.x;
+        float ay = (-1.0f - ol.y) * idl.y, by = (1.0f - ol.y) * idl.y;
+        float az = (-1.0f - ol.z) * idl.z, bz = (1.0f - ol.z) * idl.z;
+        float tnear = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+        float tfar = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+        if (!(tfar >= tmin && tnear <= tmax)) return false;
+    }
+    uint32_t id;
+    std::memcpy(&id, &rec[14], 4);
+    if (step != 0 && t < cfg.backfacing_max_dist) {  // shaders.cu:53-61 (object-space dh vs world normal, as written)
+        f3 nrm = ld3(normals, id);
+        if (sqrtf(dot3(nrm, nrm)) > cfg.backfacing_invalid_normal_threshold && dot3(nrm, dh) > 0.0f) return false;
+    }
+    float sf = rec[12], sigma = rec[13];
+    f3 x = xu * sf;                                             // shaders.cu:64
+    float d2 = dot3(x, x);
+    float g = det_exp(-det_pow(d2, cfg.exp_power) / (2.0f * cfg.exp_power));  // kernel.cu:8-12
+    float alpha = (A_MAX * g) * sigma;                          // kernel.cu:14-16
+    h.t = t;
+    h.id = (int32_t)id;
+    h.alpha = alpha;
+    h.gaussval = g;
+    h.x = x;
+    return true;
+}
+
+struct BoundSphere {
+    f3 c;
+    float r2;
+};
+
+void trace_ray(
+    const float *recs, const std::vector<BoundSphere> &bs, const float *normals, int n, const OrcConfig &cfg, int step,
+    f3 o, f3 d, float tmin, float tmax, RayResult &out) {
+    out.hits.clear();
+    out.T_full = 1.0f;
+    out.n_accepted = 0;
+    for (int i = 0; i < n; ++i) {
+        // conservative prefilter (pure accelerator): the hit point lies inside the proxy's bounding sphere
+        f3 pc = bs[i].c - o;
+        float b = dotp(pc, d);
+        float dist2 = dotp(pc, pc) - b * b;
+        if (dist2 > bs[i].r2) continue;
+        Hit h;
+        if (!candidate(recs + 16 * (size_t)i, normals, cfg, step, o, d, tmin, tmax, h)) continue;
+        out.T_full = (float)((double)out.T_full * (1.0 - (double)h.alpha));  // shaders.cu:69-71
+        out.n_accepted++;
+        out.hits.push_back(h);
+    }
+    std::sort(out.hits.begin(), out.hits.end(), [](const Hit &a, const Hit &b) {
+        return a.t < b.t || (a.t == b.t && a.id < b.id);
+    });
+}
+
+struct StepState {
+    f3 rgb, normal, f0, rem_rgb, rem_normal, rem_f0, ray_o, ray_d, throughput;
+    float depth, roughness, T, T_full, rem_depth, rem_roughness;
+    std::vector<Hit> comp;        // composited hits in composite order
+    std::vector<float> comp_T;    // transmittance after each composited hit
+    f3 used_o, used_d;
+    bool executed;
+};
+
+}  // namespace
+
+extern "C" {
+
+// Full render of one view: forward for all steps, then (grads on) the backward, else accumulate + write.
+// `total_num_calls` is the value AFTER the per-call increment (metadata.h:30), i.e. what the kernel reads.
+void orc_render(
+    const OrcScene *sc, const OrcConfig *cfgp, const OrcCamera *cam, int width, int height, uint32_t total_num_calls,
+    int grads_enabled, const OrcTargets *tg, OrcOutputs *out, OrcGrads *gr, OrcHitLists *hl, const OrcOverride *ov,
+    int pixel_begin, int pixel_end) {
+    const OrcConfig cfg = *cfgp;
+    const int n = sc->n;
+    const int P = width * height;
+    const int S = cfg.max_bounces + 1;
+    if (pixel_end <= 0 || pixel_end > P) pixel_end = P;
+    if (pixel_begin < 0) pixel_begin = 0;
+
+    std::vector<float> own_recs;
+    const float *recs = ov && ov->records ? ov->records : nullptr;
+    if (!recs) {
+        own_recs.resize((size_t)n * 16);
+        orc_prepare(sc, &cfg, own_recs.data());
+        recs = own_recs.data();
+    }
+    std::vector<BoundSphere> bs(n);
+    for (int i = 0; i < n; ++i) {
+        const float *r = recs + 16 * (size_t)i;
+        bs[i].c = mk(r[3], r[7], r[11]);
+        if (r[15] == 0.0f) {
+            bs[i].r2 = -1.0f;
+            continue;
+        }
+        // rows of W have norm 1/S_r; the unit box maps into a sphere of radius sqrt(3)*max S
+        float smax = 0.0f;
+        for (int rr = 0; rr < 3; ++rr) {
+            float nr = sqrtf(r[4 * rr] * r[4 * rr] + r[4 * rr + 1] * r[4 * rr + 1] + r[4 * rr + 2] * r[4 * rr + 2]);
+            smax = fmaxf(smax, 1.0f / nr);
+        }
+        float rad = 1.7320508f * smax * 1.001f + 1e-6f;
+        bs[i].r2 = rad * rad;
+    }
+
+    std::vector<double> A_rgb, A_normal, A_f0, A_rough, A_opac, A_scale, A_mean, A_rot, A_weight;
+    if (grads_enabled) {
+        A_rgb.assign((size_t)n * 3, 0), A_normal.assign((size_t)n * 3, 0), A_f0.assign((size_t)n * 3, 0);
+        A_rough.assign(n, 0), A_opac.assign(n, 0), A_scale.assign((size_t)n * 3, 0), A_mean.assign((size_t)n * 3, 0);
+        A_rot.assign((size_t)n * 4, 0), A_weight.assign(n, 0);
+    }
+    const int B = std::min(cfg.num_bounces, cfg.max_bounces);  // shaders.cu:85
+    const f3 cam_o = mk(cam->origin[0], cam->origin[1], cam->origin[2]);
+    // rows of rotation_w2c = columns of rotation_c2w (camera.h:62-68)
+    const f3 w2c0 = mk(cam->rot_c2w[0], cam->rot_c2w[3], cam->rot_c2w[6]);
+    const f3 w2c1 = mk(cam->rot_c2w[1], cam->rot_c2w[4], cam->rot_c2w[7]);
+    const f3 w2c2 = mk(cam->rot_c2w[2], cam->rot_c2w[5], cam->rot_c2w[8]);
+
+#pragma omp parallel
+    {
+        RayResult rr;
+        std::vector<StepState> st(S);
+#pragma omp for schedule(dynamic, 16)
+        for (int pix = pixel_begin; pix < pixel_end; ++pix) {
+            const int ix = pix % width, iy = pix / width;
+            uint32_t seed = tea4((uint32_t)pix, total_num_calls);  // shaders.cu:88
+            // primary ray (camera.h:17-36)
+            float view_size = tanf(cam->fovy / 2);
+            float aspect = (float)width / (float)height;
+            float fx = (float)ix, fy = (float)iy;
+            if (cfg.jitter_primary_rays) {
+                float jx = rnd(seed) - 0.5f;
+                float jy = rnd(seed) - 0.5f;
+                fx += jx, fy += jy;
+            }
+            float y = view_size * (1.0f - 2.0f * (fy + 1.0f / 2.0f) / (float)height);
+            float x = aspect * view_size * (2.0f * (fx + 1.0f / 2.0f) / (float)width - 1.0f);
+            f3 ray_o = cam_o;
+            f3 ray_d = normalize(w2c0 * x + w2c1 * y - w2c2);
+
+            for (int s = 0; s < S; ++s) {  // Pixel ctor, framebuffer.h:40-68
+                StepState &q = st[s];
+                q.rgb = q.normal = q.f0 = q.rem_rgb = q.rem_normal = q.rem_f0 = q.ray_o = q.ray_d = mk(0, 0, 0);
+                q.throughput = mk(1, 1, 1);
+                q.depth = q.roughness = q.rem_depth = q.rem_roughness = 0.0f;
+                q.T = q.T_full = 1.0f;
+                q.comp.clear(), q.comp_T.clear();
+                q.used_o = q.used_d = mk(0, 0, 0);
+                q.executed = false;
+            }
+            int num_hits[16] = {0};
+            int total_effective_steps = 0;
+            int last_accumulated = 0, sum_accepted = 0, sum_comp = 0;
+
+            for (int step = 0; step < B + 1; ++step) {  // shaders.cu:104
+                if (ov && ov->step_executed && !ov->step_executed[(size_t)step * P + pix]) break;
+                if (ov && ov->ray_origin) {
+                    ray_o = ld3(ov->ray_origin, (size_t)step * P + pix);
+                    ray_d = ld3(ov->ray_direction, (size_t)step * P + pix);
+                }
+                total_effective_steps++;
+                StepState &q = st[step];
+                q.executed = true;
+                q.used_o = ray_o, q.used_d = ray_d;
+                // ---- forward_pass (forward_pass.cu:3-156)
+                const float tmin0 = step != 0 ? 0.0f : cam->znear;
+                const float tmax = cam->zfar;
+                trace_ray(recs, bs, sc->normal, n, cfg, step, ray_o, ray_d, tmin0, tmax, rr);
+                q.T = 1.0f;
+                q.T_full = rr.T_full;
+                sum_accepted += rr.n_accepted;
+                float w = tmin0;
+                size_t pos = 0;
+                int total_acc = 0;
+                const size_t H = rr.hits.size();
+                for (int it = 0; it < MAX_ITERATIONS && w < tmax; ++it) {
+                    // the (up to) 16 nearest hits with t > w, strictly (forward_pass.cu:62)
+                    while (pos < H && !(rr.hits[pos].t > w)) ++pos;
+                    if (pos >= H) break;  // forward_pass.cu:80-83
+                    size_t endb = std::min(H, pos + (size_t)BUFFER_SIZE);
+                    bool stop = false;
+                    for (size_t i = pos; i < endb; ++i) {
+                        const Hit &h = rr.hits[i];
+                        w = fmaxf(w, h.t);
+                        if (h.t < tmax) {
+                            num_hits[step]++;
+                            total_acc++;
+                            uint32_t id = (uint32_t)h.id;
+                            f3 c_rgb = ld3(sc->rgb, id);
+                            c_rgb = mk(fmaxf(0.0f, c_rgb.x), fmaxf(0.0f, c_rgb.y), fmaxf(0.0f, c_rgb.z));
+                            f3 c_n = ld3(sc->normal, id);
+                            f3 c_f0 = ld3(sc->f0, id);
+                            c_f0 = mk(fminf(fmaxf(0.0f, c_f0.x), 1.0f), fminf(fmaxf(0.0f, c_f0.y), 1.0f),
+                                      fminf(fmaxf(0.0f, c_f0.z), 1.0f));
+                            float c_r = fminf(fmaxf(0.0f, sc->roughness[id]), 1.0f);
+                            float nextT = q.T * (1.0f - h.alpha);  // forward_pass.cu:108-115
+                            float wt = q.T - nextT;
+                            q.rgb = q.rgb + c_rgb * wt;
+                            q.normal = q.normal + c_n * wt;
+                            q.f0 = q.f0 + c_f0 * wt;
+                            q.roughness += c_r * wt;
+                            q.depth += h.t * wt;
+                            q.T = nextT;
+                            q.comp.push_back(h);
+                            q.comp_T.push_back(q.T);
+                            if (q.T < cfg.transmittance_threshold) {  // forward_pass.cu:131-134
+                                w = tmax;
+                                stop = true;
+                                break;
+                            }
+                        }
+                    }
+                    if (stop) break;
+                    // a batch with an empty slot drives the window to FLT_MAX through the fill value
+                    // (forward_pass.cu:56,89), which ends the loop
+                    if (endb - pos < (size_t)BUFFER_SIZE) break;
+                    pos = endb;
+                }
+                last_accumulated = total_acc;
+                sum_comp += total_acc;
+                // remaining fill (forward_pass.cu:143-155)
+                float rem_T = q.T - q.T_full;
+                float nrm = fmaxf(1.0f - q.T, cfg.eps_forward_normalization);
+                q.rem_rgb = div_s(q.rgb, nrm);
+                q.rgb = q.rgb + rem_T * q.rem_rgb;
+                q.rem_depth = q.depth / nrm;
+                q.depth = q.depth + rem_T * q.rem_depth;
+                q.rem_normal = div_s(q.normal, nrm);
+                q.normal = q.normal + rem_T * q.rem_normal;
+                q.rem_f0 = div_s(q.f0, nrm);
+                q.f0 = q.f0 + rem_T * q.rem_f0;
+                q.rem_roughness = q.roughness / nrm;
+                q.roughness = q.roughness + rem_T * q.rem_roughness;
+
+                if (step > 0) q.rgb = q.rgb * st[step - 1].throughput;  // shaders.cu:112-114
+                f3 un = q.normal;
+                f3 en = normalize(un);
+                float er = fmaxf(q.roughness, cfg.eps_min_roughness);
+                if (length(un) < cfg.reflection_invalid_normal_threshold) break;  // shaders.cu:123-125
+                f3 epos = ray_o + q.depth * ray_d;
+                // sample_cook_torrance (ggx_brdf.h:152-168); argument order u1 then u2
+                float u1 = rnd(seed);
+                float u2 = rnd(seed);
+                f3 V = -ray_d;
+                float a = er * er;
+                float phi = (float)(2.0f * M_PI * (double)u1);
+                float cosT = sqrtf((1.0f - u2) / (1.0f + (a * a - 1.0f) * u2));
+                float sinT = sqrtf(1.0f - cosT * cosT);
+                f3 Hl = mk(sinT * cosf(phi), sinT * sinf(phi), cosT);
+                f3 Tn = normalize(cross(en.z < 0.999f ? mk(0, 0, 1) : mk(1, 0, 0), en));
+                f3 Bn = cross(en, Tn);
+                f3 Hh = Hl.x * Tn + Hl.y * Bn + Hl.z * en;
+                f3 inc = -V;
+                f3 next_d = inc - 2.0f * Hh * dotp(Hh, inc);  // reflect(-V,H), vec_math.h:385
+                f3 next_o = epos + cfg.eps_ray_surface_offset * next_d;
+                f3 ef0 = q.f0;
+                if (step > 0) q.throughput = st[step - 1].throughput;
+                // cook_torrance_weight (ggx_brdf.h:134-150)
+                f3 wgt = mk(0, 0, 0);
+                if (!(ef0.x == 0.0f && ef0.y == 0.0f && ef0.z == 0.0f)) {
+                    f3 L = next_d;
+                    f3 Hn = normalize(V + L);
+                    float NdotH = fmaxf(dotp(en, Hn), 0.0f);
+                    float VdotH = fmaxf(dotp(V, Hn), 0.0f);
+                    float NdotV = fmaxf(dotp(en, V), 0.0f);
+                    float al = er * er;
+                    auto G1 = [&](f3 Wv) {
+                        float NdotW = fmaxf(dotp(en, Wv), 0.0f);
+                        float kk = (al * al) / 2.0f;
+                        return (float)(NdotW / ((double)(NdotW * (1.0f - kk) + kk) + 1e-8));
+                    };
+                    float G = G1(V) * G1(L);
+                    float pw = 1.0f - VdotH;
+                    float p5 = pw * pw;
+                    p5 = p5 * p5 * pw;
+                    f3 F = ef0 + (mk(1, 1, 1) - ef0) * p5;
+                    // float3 / double resolves to operator/(float3, float): the denominator is rounded to
+                    // float and the numerator multiplied by its reciprocal (vec_math.h:330-333)
+                    float den = (float)((double)(NdotH * NdotV) + 1e-8);
+                    wgt = div_s(F * G * VdotH, den);
+                }
+                q.throughput = q.throughput * wgt;
+                ray_o = next_o, ray_d = next_d;
+                q.ray_o = ray_o, q.ray_d = ray_d;
+            }
+            f3 fin = mk(0, 0, 0);
+            for (int step = 0; step < B + 1; ++step) fin = fin + st[step].rgb;  // shaders.cu:150-152
+
+            if (out->num_accumulated) out->num_accumulated[pix] = last_accumulated;
+            if (out->num_hits_per_pixel) out->num_hits_per_pixel[pix] = sum_accepted;
+            if (out->num_composited_per_pixel) out->num_composited_per_pixel[pix] = sum_comp;
+            if (out->num_steps_per_pixel) out->num_steps_per_pixel[pix] = total_effective_steps;
+            for (int s = 0; s < S; ++s) {
+                size_t o_ = (size_t)s * P + pix;
+                if (out->used_ray_origin) st3(out->used_ray_origin, o_, st[s].used_o);
+                if (out->used_ray_direction) st3(out->used_ray_direction, o_, st[s].used_d);
+                if (out->step_executed) out->step_executed[o_] = st[s].executed ? 1 : 0;
+                if (hl && hl->cap > 0) {
+                    hl->counts[o_] = (int32_t)st[s].comp.size();
+                    for (int k = 0; k < hl->cap; ++k) {
+                        bool have = k < (int)st[s].comp.size();
+                        hl->ids[o_ * hl->cap + k] = have ? st[s].comp[k].id : -1;
+                        if (hl->ts) hl->ts[o_ * hl->cap + k] = have ? st[s].comp[k].t : 0.0f;
+                    }
+                }
+            }
+
+            if (grads_enabled) {
+                // ---- backward (shaders.cu:155-162, backward_pass.cu:3-222)
+                f3 t_diff = ld3(tg->diffuse, pix), t_spec = ld3(tg->specular, pix), t_n = ld3(tg->normal, pix),
+                   t_f0 = ld3(tg->f0, pix);
+                float t_depth = tg->depth[pix], t_rough = tg->roughness[pix];
+                const float kexp = cfg.exp_power;
+                for (int step = total_effective_steps - 1; step >= 0; --step) {
+                    if (num_hits[step] <= 0) continue;
+                    StepState &q = st[step];
+                    f3 thr = step == 0 ? mk(1, 1, 1) : st[step - 1].throughput;
+                    float rdw = powf(1.0f - st[std::max(step - 1, 0)].roughness, ROUGH_DOWNWEIGHT_POW);
+                    f3 d_rgb = mk(0, 0, 0), d_n = mk(0, 0, 0), d_f0 = mk(0, 0, 0);
+                    float d_depth = 0.0f, d_rough = 0.0f;
+                    if (step == 0) {  // backward_pass.cu:89-99
+                        d_rgb = 1.0f / 3.0f * sign3(st[0].rgb - t_diff) * cfg.loss_weight_diffuse;
+                        d_depth = sign1(st[0].depth - t_depth) * cfg.loss_weight_depth;
+                        d_n = 1.0f / 3.0f * sign3(st[0].normal - t_n) * cfg.loss_weight_normal;
+                        d_f0 = 1.0f / 3.0f * sign3(st[0].f0 - t_f0) * cfg.loss_weight_f0;
+                        d_rough = sign1(st[0].roughness - t_rough) * cfg.loss_weight_roughness;
+                    } else {  // backward_pass.cu:100-108
+                        f3 spec = mk(0, 0, 0);
+                        for (int j = 1; j < B + 1; ++j) spec = spec + st[j].rgb;
+                        d_rgb = 1.0f / 3.0f * sign3(spec - t_spec) * cfg.loss_weight_specular * rdw;
+                        d_rgb = d_rgb * thr;
+                    }
+                    f3 p_rgb = mk(0, 0, 0), w_rgb = mk(0, 0, 0), p_n = mk(0, 0, 0), w_n = mk(0, 0, 0),
+                       p_f0 = mk(0, 0, 0), w_f0 = mk(0, 0, 0);
+                    float p_r = 0, w_r = 0, p_d = 0, w_d = 0;
+                    for (int hi = (int)q.comp.size() - 1; hi >= 0; --hi) {  // farthest -> nearest
+                        const Hit &h = q.comp[hi];
+                        const uint32_t id = (uint32_t)h.id;
+                        const float Tr = q.comp_T[hi];
+                        const float alpha = h.alpha, gv = h.gaussval;
+                        f3 c_rgb = ld3(sc->rgb, id);
+                        c_rgb = mk(fmaxf(0.0f, c_rgb.x), fmaxf(0.0f, c_rgb.y), fmaxf(0.0f, c_rgb.z));
+                        f3 c_n = mk(0, 0, 0), c_f0 = mk(0, 0, 0);
+                        float c_r = 0.0f;
+                        if (step == 0) {
+                            c_n = ld3(sc->normal, id);
+                            c_f0 = ld3(sc->f0, id);
+                            c_f0 = mk(fminf(fmaxf(0.0f, c_f0.x), 1.0f), fminf(fmaxf(0.0f, c_f0.y), 1.0f),
+                                      fminf(fmaxf(0.0f, c_f0.z), 1.0f));
+                            c_r = fminf(fmaxf(0.0f, sc->roughness[id]), 1.0f);
+                        }
+                        const float *rec = recs + 16 * (size_t)id;
+                        float sigma = rec[13], sf = rec[12];
+                        f3 sc_e = mk(expf(sc->scale[3 * id]), expf(sc->scale[3 * id + 1]), expf(sc->scale[3 * id + 2]));
+                        float qr = sc->rotation[4 * id], qx = sc->rotation[4 * id + 1], qy = sc->rotation[4 * id + 2],
+                              qz = sc->rotation[4 * id + 3];
+                        float qn = sqrtf(qr * qr + qx * qx + qy * qy + qz * qz);
+                        float r = qr / qn, xq = qx / qn, yq = qy / qn, zq = qz / qn;
+                        // colour gradients (backward_pass.cu:110-115); activations' backward is always open
+                        // because it is evaluated on the activated value (activations.cu:42,54-56)
+                        float weight = (float)((double)Tr / (1.0 - (double)alpha) * (double)alpha);
+                        f3 g_c = d_rgb * weight;
+                        f3 g_nn = d_n * weight;
+                        f3 g_ff = d_f0 * weight;
+                        float g_rr = d_rough * weight;
+                        w_rgb = w_rgb + (c_rgb - p_rgb) * Tr, p_rgb = c_rgb;
+                        if (step == 0) {
+                            w_n = w_n + (c_n - p_n) * Tr, p_n = c_n;
+                            w_f0 = w_f0 + (c_f0 - p_f0) * Tr, p_f0 = c_f0;
+                            w_r += (c_r - p_r) * Tr, p_r = c_r;
+                            w_d += (h.t - p_d) * Tr, p_d = h.t;
+                        }
+                        float dL_da = 0.0f;
+                        float tmp1 = 1.0f / (1.0f - alpha);
+                        dL_da += dotp(w_rgb * tmp1, d_rgb);
+                        dL_da += dotp(w_n * tmp1, d_n);
+                        dL_da += dotp(w_f0 * tmp1, d_f0);
+                        dL_da += (w_r * tmp1) * d_rough;
+                        dL_da += (w_d * tmp1) * d_depth;
+                        float tmp2 = -((q.T - q.T_full) / (1.0f - alpha));
+                        dL_da += tmp2 * dotp(q.rem_rgb, d_rgb);
+                        dL_da += tmp2 * dotp(q.rem_normal, d_n);
+                        dL_da += tmp2 * dotp(q.rem_f0, d_f0);
+                        dL_da += tmp2 * (q.rem_roughness * d_rough);
+                        dL_da += tmp2 * (q.rem_depth * d_depth);
+                        float g_op = A_MAX * dL_da * gv;
+                        g_op = g_op * sigma * (1.0f - sigma);  // activations.cu:8
+                        float dL_dg = A_MAX * dL_da * sigma;
+                        float sqn = dotp(h.x, h.x);
+                        float dsq = gv * det_pow(sqn, kexp - 1.0f);  // backward_pass.cu:157
+                        f3 dxl = -h.x * dsq * dL_dg;
+                        // world_to_local columns dotted with dxl (backward_pass.cu:160-167)
+                        f3 w0 = mk(rec[0], rec[1], rec[2]), w1 = mk(rec[4], rec[5], rec[6]), w2 = mk(rec[8], rec[9], rec[10]);
+                        f3 dxw = mk(dotp(mk(w0.x, w1.x, w2.x), dxl), dotp(mk(w0.y, w1.y, w2.y), dxl),
+                                    dotp(mk(w0.z, w1.z, w2.z), dxl)) *
+                                 sf;
+                        f3 l0 = -dxw.x * h.x, l1 = -dxw.y * h.x, l2 = -dxw.z * h.x;
+                        f3 g_mean = -dxw;
+                        // local_to_world rows: M[r][c] = R[r][c] * s_c * sf * global (bvh_wrapper.cu:25-30)
+                        float Rm[3][3] = {
+                            {1.f - 2.f * (yq * yq + zq * zq), 2.f * (xq * yq - r * zq), 2.f * (xq * zq + r * yq)},
+                            {2.f * (xq * yq + r * zq), 1.f - 2.f * (xq * xq + zq * zq), 2.f * (yq * zq - r * xq)},
+                            {2.f * (xq * zq - r * yq), 2.f * (yq * zq + r * xq), 1.f - 2.f * (xq * xq + yq * yq)}};
+                        f3 Sg = sc_e * sf * cfg.global_scale_factor;
+                        f3 den = sc_e * sf + mk(cfg.eps_scale_grad, cfg.eps_scale_grad, cfg.eps_scale_grad);
+                        f3 rot0 = mk(Rm[0][0] * Sg.x, Rm[0][1] * Sg.y, Rm[0][2] * Sg.z) / den;
+                        f3 rot1 = mk(Rm[1][0] * Sg.x, Rm[1][1] * Sg.y, Rm[1][2] * Sg.z) / den;
+                        f3 rot2 = mk(Rm[2][0] * Sg.x, Rm[2][1] * Sg.y, Rm[2][2] * Sg.z) / den;
+                        f3 g_scale = (l0 * rot0 + l1 * rot1 + l2 * rot2) * sc_e;  // backward_exp_act
+                        f3 dr0 = l0 * sc_e, dr1 = l1 * sc_e, dr2 = l2 * sc_e;
+                        float dLr = 2.f * xq * (dr2.y - dr1.z) + 2.f * yq * (dr0.z - dr2.x) + 2.f * zq * (dr1.x - dr0.y);
+                        float dLx = -4.f * xq * (dr1.y + dr2.z) + 2.f * yq * (dr0.y + dr1.x) + 2.f * zq * (dr0.z + dr2.x) +
+                                    2.f * r * (dr2.y - dr1.z);
+                        float dLy = 2.f * xq * (dr0.y + dr1.x) - 4.f * yq * (dr0.x + dr2.z) + 2.f * zq * (dr1.z + dr2.y) +
+                                    2.f * r * (dr0.z - dr2.x);
+                        float dLz = 2.f * xq * (dr0.z + dr2.x) + 2.f * yq * (dr1.z + dr2.y) - 4.f * zq * (dr0.x + dr1.y) +
+                                    2.f * r * (dr1.x - dr0.y);
+                        // backward_normalize_act (activations.cu:71-73): dot(dL,x)*(-x)/|x|^3 + dL/|x|
+                        float dq = dLr * qr + dLx * qx + dLy * qy + dLz * qz;
+                        float i3 = 1.0f / powf(qn, 3.0f), i1 = 1.0f / qn;  // float4 / float = times reciprocal
+                        float gq[4] = {(dq * -qr) * i3 + dLr * i1, (dq * -qx) * i3 + dLx * i1, (dq * -qy) * i3 + dLy * i1,
+                                       (dq * -qz) * i3 + dLz * i1};
+#pragma omp atomic
+                        A_opac[id] += g_op;
+                        float gs3[3] = {g_scale.x, g_scale.y, g_scale.z}, gm3[3] = {g_mean.x, g_mean.y, g_mean.z},
+                              gc3[3] = {g_c.x, g_c.y, g_c.z}, gn3[3] = {g_nn.x, g_nn.y, g_nn.z},
+                              gf3[3] = {g_ff.x, g_ff.y, g_ff.z};
+                        for (int c = 0; c < 3; ++c) {
+#pragma omp atomic
+                            A_scale[3 * (size_t)id + c] += gs3[c];
+#pragma omp atomic
+                            A_mean[3 * (size_t)id + c] += gm3[c];
+#pragma omp atomic
+                            A_rgb[3 * (size_t)id + c] += gc3[c];
+                        }
+                        for (int c = 0; c < 4; ++c) {
+#pragma omp atomic
+                            A_rot[4 * (size_t)id + c] += gq[c];
+                        }
+                        if (step == 0) {
+                            for (int c = 0; c < 3; ++c) {
+#pragma omp atomic
+                                A_normal[3 * (size_t)id + c] += gn3[c];
+#pragma omp atomic
+                                A_f0[3 * (size_t)id + c] += gf3[c];
+                            }
+#pragma omp atomic
+                            A_rough[id] += g_rr;
+                        }
+#pragma omp atomic
+                        A_weight[id] += weight;
+                    }
+                }
+            } else {
+                // ---- accumulate + write (shaders.cu:163-169, framebuffer.h:104-143), all S steps
+                if (cfg.accumulate_samples) {
+                    int cnt = *out->acc_count;
+                    float dv = (float)(cnt + 1);
+                    fin = mk(0, 0, 0);
+                    for (int s = 0; s < S; ++s) {
+                        size_t o_ = (size_t)pix + (size_t)P * s;
+                        StepState &q = st[s];
+                        f3 a3 = ld3(out->acc_rgb, o_) + q.rgb;
+                        st3(out->acc_rgb, o_, a3), q.rgb = div_s(a3, dv);
+                        out->acc_transmittance[o_] += q.T, q.T = out->acc_transmittance[o_] / dv;
+                        out->acc_total_transmittance[o_] += q.T_full, q.T_full = out->acc_total_transmittance[o_] / dv;
+                        out->acc_depth[o_] += q.depth, q.depth = out->acc_depth[o_] / dv;
+                        a3 = ld3(out->acc_normal, o_) + q.normal;
+                        st3(out->acc_normal, o_, a3), q.normal = div_s(a3, dv);
+                        a3 = ld3(out->acc_f0, o_) + q.f0;
+                        st3(out->acc_f0, o_, a3), q.f0 = div_s(a3, dv);
+                        out->acc_roughness[o_] += q.roughness, q.roughness = out->acc_roughness[o_] / dv;
+                        fin = fin + q.rgb;
+                    }
+                }
+                for (int s = 0; s < S; ++s) {
+                    size_t o_ = (size_t)pix + (size_t)P * s;
+                    const StepState &q = st[s];
+                    if (out->rgb) st3(out->rgb, o_, q.rgb);
+                    if (out->depth) out->depth[o_] = q.depth;
+                    if (out->normal) st3(out->normal, o_, q.normal);
+                    if (out->f0) st3(out->f0, o_, q.f0);
+                    if (out->roughness) out->roughness[o_] = q.roughness;
+                    if (out->transmittance) out->transmittance[o_] = q.T;
+                    if (out->total_transmittance) out->total_transmittance[o_] = q.T_full;
+                    if (out->ray_origin) st3(out->ray_origin, o_, q.ray_o);
+                    if (out->ray_direction) st3(out->ray_direction, o_, q.ray_d);
+                }
+                if (out->final_) st3(out->final_, pix, fin);
+            }
+            if (out->random_seeds) out->random_seeds[pix] = seed;  // shaders.cu:172
+        }
+    }
+    if (grads_enabled) {
+        for (size_t i = 0; i < (size_t)n; ++i) {
+            for (int c = 0; c < 3; ++c) {
+                gr->dL_drgb[3 * i + c] += (float)A_rgb[3 * i + c];
+                gr->dL_dnormal[3 * i + c] += (float)A_normal[3 * i + c];
+                gr->dL_df0[3 * i + c] += (float)A_f0[3 * i + c];
+                gr->dL_dscale[3 * i + c] += (float)A_scale[3 * i + c];
+                gr->dL_dmean[3 * i + c] += (float)A_mean[3 * i + c];
+            }
+            for (int c = 0; c < 4; ++c) gr->dL_drotation[4 * i + c] += (float)A_rot[4 * i + c];
+            gr->dL_droughness[i] += (float)A_rough[i];
+            gr->dL_dopacity[i] += (float)A_opac[i];
+            gr->total_weight[i] += (float)A_weight[i];
+        }
+    }
+}
+
+}  // extern "C"
