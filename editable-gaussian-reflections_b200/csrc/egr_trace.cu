@@ -116,6 +116,12 @@ __global__ void __launch_bounds__(256) k_begin(TraceCtx c, int grads) {
         c.p.stats.num_steps_per_pixel[i] = 0;
         c.steps_executed[i] = 0;
     }
+    // every (warp tile, step) starts without a hit log; tiles whose rays all died never touch their entry
+    const uint32_t nt = c.num_warps * c.S;
+    for (uint32_t k = i; k < nt; k += gridDim.x * blockDim.x) {
+        c.warp_tail[2 * (size_t)k] = 0xFFFFFFFFu;
+        c.warp_tail[2 * (size_t)k + 1] = 0u;
+    }
 }
 __global__ void k_end(TraceCtx c) {  // raytracer.cpp:91-93 without the host sync
     if (threadIdx.x == 0 && blockIdx.x == 0 && *c.p.config.accumulate_samples)
@@ -326,7 +332,7 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
         const float a = er * er;
         const float phi = (float)(2.0f * 3.14159265358979323846 * (double)u1);
         const float cosT = sqrtf((1.0f - u2) / (1.0f + (a * a - 1.0f) * u2));
-        const float sinT = sqrtf(1.0f - cosT * cosT);
+        const float sinT = sqrtf(fmaf(-cosT, cosT, 1.0f));
         float sp, cp;
         sincosf(phi, &sp, &cp);
         const f3 Hl = mk3(sinT * cp, sinT * sp, cosT);

@@ -508,7 +508,7 @@ void orc_render(
                 float a = er * er;
                 float phi = (float)(2.0f * M_PI * (double)u1);
                 float cosT = sqrtf((1.0f - u2) / (1.0f + (a * a - 1.0f) * u2));
-                float sinT = sqrtf(1.0f - cosT * cosT);
+                float sinT = sqrtf(fmaf(-cosT, cosT, 1.0f));  // nvcc contracts 1 - c*c (ggx_brdf.h:158) into one fma
                 f3 Hl = mk(sinT * cosf(phi), sinT * sinf(phi), cosT);
                 f3 Tn = normalize(cross(en.z < 0.999f ? mk(0, 0, 1) : mk(1, 0, 0), en));
                 f3 Bn = cross(en, Tn);
