@@ -60,6 +60,13 @@ EGR_ABI_VERSION = 1
 EGR_MAX_STEPS = 8
 EGR_GRAD_STRIDE = 24
 EGR_RECORD_FLOATS = 16
+EGR_PHASE_BEGIN = 0x1
+EGR_PHASE_FINISH = 0x10000
+EGR_PHASE_ALL = 0xFFFFFFFF
+
+
+def EGR_PHASE_STEP(s: int) -> int:
+    return 0x2 << s
 
 # every symbol include/egr_b200.h declares: (restype, argtypes)
 SYMBOLS = {
@@ -77,6 +84,7 @@ SYMBOLS = {
     "egr_pixel_state_bytes": (C.c_size_t, [C.c_uint32, C.c_uint32, C.c_uint32]),
     "egr_hitlog_bytes_for_hits": (C.c_size_t, [C.c_uint64]),
     "egr_raytrace": (C.c_int, [C.POINTER(EgrParams), C.c_int, _FP]),
+    "egr_raytrace_phases": (C.c_int, [C.POINTER(EgrParams), C.c_int, C.c_uint32, _FP]),
     "egr_reset_accumulators": (C.c_int, [C.POINTER(EgrParams), _FP]),
     "egr_denoise_passthrough": (C.c_int, [C.POINTER(EgrParams), _FP]),
     "egr_hitlog_export": (C.c_int, [C.POINTER(EgrParams), C.c_int, C.c_int, _FP, _FP, _FP, _FP]),

@@ -469,7 +469,7 @@ extern "C" size_t egr_hitlog_bytes_for_hits(uint64_t hits) {
     return (size_t)((hits + 511) / 512) * HITLOG_CHUNK_BYTES;
 }
 
-extern "C" int egr_raytrace(const EgrParams *p, int grads_enabled, void *stream) {
+extern "C" int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32_t phase_mask, void *stream) {
     TraceCtx c;
     int rc = make_ctx(p, c);
     if (rc) return rc;
@@ -482,20 +482,29 @@ extern "C" int egr_raytrace(const EgrParams *p, int grads_enabled, void *stream)
         set_error("grads enabled but no hit log was provided");
         return EGR_EINVAL;
     }
-    rc = launch_pack_appearance(c.bvh, p->gaussians, st);
-    if (rc) return rc;
-    k_begin<<<(c.P + 255) / 256, 256, 0, st>>>(c, grads_enabled);
-    const uint32_t blocks = (c.num_warps + 3) / 4;
-    for (uint32_t s = 0; s < c.S; ++s) k_trace_step<<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
-    if (grads_enabled) {
-        rc = launch_backward_impl(c, st);
+    if (phase_mask & EGR_PHASE_BEGIN) {
+        rc = launch_pack_appearance(c.bvh, p->gaussians, st);
         if (rc) return rc;
-    } else {
-        k_resolve<<<(c.P + 255) / 256, 256, 0, st>>>(c);
+        k_begin<<<(c.P + 255) / 256, 256, 0, st>>>(c, grads_enabled);
     }
-    k_end<<<1, 32, 0, st>>>(c);
+    const uint32_t blocks = (c.num_warps + 3) / 4;
+    for (uint32_t s = 0; s < c.S; ++s)
+        if (phase_mask & EGR_PHASE_STEP(s)) k_trace_step<<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
+    if (phase_mask & EGR_PHASE_FINISH) {
+        if (grads_enabled) {
+            rc = launch_backward_impl(c, st);
+            if (rc) return rc;
+        } else {
+            k_resolve<<<(c.P + 255) / 256, 256, 0, st>>>(c);
+        }
+        k_end<<<1, 32, 0, st>>>(c);
+    }
     EGR_CUDA_TRY(cudaGetLastError());
     return EGR_OK;
+}
+
+extern "C" int egr_raytrace(const EgrParams *p, int grads_enabled, void *stream) {
+    return egr_raytrace_phases(p, grads_enabled, EGR_PHASE_ALL, stream);
 }
 
 extern "C" int egr_hitlog_export(const EgrParams *p, int step, int cap, int32_t *ids, float *ts, int32_t *counts,

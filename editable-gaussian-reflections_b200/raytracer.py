@@ -325,13 +325,22 @@ class Raytracer:
         self._params = p
 
     # ---- methods (raytracer.cpp:81-120) ------------------------------------------------------------------
-    def raytrace(self):
-        grads = torch.is_grad_enabled()  # metadata.h:29
+    def _ensure_hitlog(self, grads):
         if grads and self._hitlog is None:
             nbytes = self._lib.egr_hitlog_bytes_for_hits(self._hitlog_capacity_hits)
             self._hitlog = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self._dev)
             self._build_params()
+
+    def raytrace(self):
+        grads = torch.is_grad_enabled()  # metadata.h:29
+        self._ensure_hitlog(grads)
         _capi.check(self._lib.egr_raytrace(C.byref(self._params), int(grads), self._stream()))
+
+    def raytrace_phases(self, phase_mask):
+        """raytrace() split into its launches (not in the reference; used by bench.py to time single kernels)."""
+        grads = torch.is_grad_enabled()
+        self._ensure_hitlog(grads)
+        _capi.check(self._lib.egr_raytrace_phases(C.byref(self._params), int(grads), int(phase_mask), self._stream()))
 
     def denoise(self):
         """OptiX AI denoiser is unavailable (proprietary driver network): documented pass-through."""

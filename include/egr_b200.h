@@ -165,6 +165,14 @@ size_t egr_hitlog_bytes_for_hits(uint64_t num_hits_capacity);
  * backward (grads_enabled != 0; nothing is written to the framebuffer, shaders.cu:155-169) or accumulation +
  * output writes, and the accumulated_sample_count bump. */
 int egr_raytrace(const EgrParams *p, int grads_enabled, void *stream);
+/* The same call split into its launches so that a caller can bracket each kernel with events (bench.py times the
+ * dominant kernel this way): BEGIN = appearance pack + metadata/stats reset, STEP(s) = forward of ray-step s,
+ * FINISH = backward (grads) or resolve/write (no grads) + sample-count bump.  egr_raytrace == EGR_PHASE_ALL. */
+#define EGR_PHASE_BEGIN 0x1u
+#define EGR_PHASE_STEP(s) (0x2u << (s))
+#define EGR_PHASE_FINISH 0x10000u
+#define EGR_PHASE_ALL 0xFFFFFFFFu
+int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32_t phase_mask, void *stream);
 
 /* FramebufferDataHolder::reset_accumulators (csrc/core/framebuffer.h:249-258) as one launch. */
 int egr_reset_accumulators(const EgrParams *p, void *stream);

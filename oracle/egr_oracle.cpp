@@ -179,6 +179,11 @@ struct OrcOverride {  // optional: trace these rays instead of the oracle's own 
     const float *records;                     // [N,16] packed geometry records, layout of orc_prepare
 };
 
+// test hooks for the integer-exact / IEEE-only building blocks
+float orc_det_exp(float u) { return det_exp(u); }
+uint32_t orc_tea4(uint32_t a, uint32_t b) { return tea4(a, b); }
+float orc_rnd(uint32_t *seed) { return rnd(*seed); }
+
 int orc_num_threads() {
 #ifdef _OPENMP
     return omp_get_max_threads();

@@ -117,6 +117,12 @@ def lib():
         build()
         _lib = C.CDLL(_LIB_PATH)
         _lib.orc_num_threads.restype = C.c_int
+        _lib.orc_det_exp.restype = C.c_float
+        _lib.orc_det_exp.argtypes = [C.c_float]
+        _lib.orc_tea4.restype = C.c_uint32
+        _lib.orc_tea4.argtypes = [C.c_uint32, C.c_uint32]
+        _lib.orc_rnd.restype = C.c_float
+        _lib.orc_rnd.argtypes = [C.POINTER(C.c_uint32)]
         _lib.orc_prepare.argtypes = [C.POINTER(OrcScene), C.POINTER(OrcConfig), _FP]
         _lib.orc_render.argtypes = [
             C.POINTER(OrcScene), C.POINTER(OrcConfig), C.POINTER(OrcCamera), C.c_int, C.c_int, C.c_uint32, C.c_int,

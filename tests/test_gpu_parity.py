@@ -331,3 +331,35 @@ def test_renderer_facade_train_like_iteration(small):
         pkg = egr_b200.render(view, rtr, targets_available=False)
     assert pkg.rgb.shape == (3, 3, Hh, W) and pkg.final.shape == (1, 3, Hh, W)
     assert float(pkg.rgb.abs().max()) > 0
+
+
+def test_cuda_vs_committed_reference_vectors():
+    """The CUDA path against tests/golden/ref_small.npz, i.e. against outputs of the reference's own shader
+    sources (made by tests/golden/make_golden.py): primary-step planes <= 1e-4, RNG stream exact, and the three
+    gradient tensors that only receive primary-step terms <= 1e-3 relative."""
+    import os
+
+    import torch
+
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_small.npz"))
+    W, Hh = 24, 16
+    sc = {k: g["scene_" + k] for k in scenes.PARAM_KEYS}
+    cam = dict(origin=g["cam_origin"], c2w=g["cam_c2w"], fovy=float(g["cam_fovy"]), width=W, height=Hh)
+    cfg = dict(num_bounces=2, jitter_primary_rays=True, loss_weight_diffuse=5.0, loss_weight_specular=3.0,
+               loss_weight_depth=2.5, loss_weight_normal=2.5)
+    rt = H.make_gpu_raytracer(sc, cam, cfg)
+    H.set_targets(rt, {k: g["target_" + k] for k in orc.TARGET_KEYS})
+    rt.get_metadata().total_num_calls.fill_(6)  # the fixture was made at call 7
+    with torch.no_grad():
+        rt.raytrace()
+    out = H.gpu_outputs(rt)
+    assert np.array_equal(out["random_seeds"], g["ref_random_seeds"])
+    assert np.array_equal(out["num_accumulated_per_pixel"], g["ref_num_accumulated"])
+    for k in ("rgb", "depth", "normal", "f0", "roughness", "transmittance", "total_transmittance"):
+        assert _buf_err(out[k][0], g["ref_" + k][0]) <= TOL_BUF, (k, _buf_err(out[k][0], g["ref_" + k][0]))
+    rt.get_metadata().total_num_calls.fill_(6)
+    with torch.enable_grad():
+        rt.raytrace()
+    gr = H.gpu_grads(rt)
+    for k in ("dL_dnormal", "dL_df0", "dL_droughness"):
+        assert H.rel_err(gr[k], g["ref_" + k]) <= TOL_GRAD, (k, H.rel_err(gr[k], g["ref_" + k]))
