@@ -60,6 +60,7 @@ EGR_ABI_VERSION = 1
 EGR_MAX_STEPS = 8
 EGR_GRAD_STRIDE = 24
 EGR_RECORD_FLOATS = 16
+EGR_NOALLOC_MAX_GAUSSIANS = 65536
 EGR_PHASE_BEGIN = 0x1
 EGR_PHASE_FINISH = 0x10000
 EGR_PHASE_ALL = 0xFFFFFFFF
@@ -80,6 +81,7 @@ SYMBOLS = {
     "egr_bvh_storage_bytes": (C.c_size_t, [C.c_uint32]),
     "egr_bvh_scratch_bytes": (C.c_size_t, [C.c_uint32]),
     "egr_bvh_build": (C.c_int, [C.POINTER(EgrGaussians), C.POINTER(EgrConfig), _FP, C.c_size_t, _FP, C.c_size_t, _FP]),
+    "egr_bvh_build_noalloc": (C.c_int, [C.POINTER(EgrGaussians), C.POINTER(EgrConfig), _FP, C.c_size_t, _FP]),
     "egr_bvh_refit": (C.c_int, [C.POINTER(EgrGaussians), C.POINTER(EgrConfig), _FP, C.c_size_t, _FP]),
     "egr_pixel_state_bytes": (C.c_size_t, [C.c_uint32, C.c_uint32, C.c_uint32]),
     "egr_hitlog_bytes_for_hits": (C.c_size_t, [C.c_uint64]),

@@ -4,6 +4,8 @@
 // (editable_gauss_refl/cuda/csrc/optix/bvh_wrapper.h:24-157, bvh_wrapper.cu:9-70).
 #include <cub/device/device_radix_sort.cuh>
 
+#include <mutex>
+
 #include "egr_common.cuh"
 
 namespace egr {
@@ -395,4 +397,56 @@ extern "C" int egr_bvh_export(const void *storage, size_t storage_bytes, uint32_
     if (nodes) EGR_CUDA_TRY(cudaMemcpyAsync(nodes, v.nodes, (size_t)L.num_nodes * 32, cudaMemcpyDeviceToDevice, st));
     if (parents) EGR_CUDA_TRY(cudaMemcpyAsync(parents, v.parents, (size_t)L.num_nodes * 4, cudaMemcpyDeviceToDevice, st));
     return EGR_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Allocation-free rebuild
+// ---------------------------------------------------------------------------------------------------------
+// Build scratch for egr_bvh_build_noalloc(): a fixed block inside the library image, so a rebuild needs no device
+// allocation from anybody.  Every GPU that loads the library carries these 6 MiB until the process exits.
+static constexpr size_t kNoAllocScratchBytes = 6u << 20;
+static __device__ __align__(256) unsigned char g_noalloc_build_scratch[kNoAllocScratchBytes];
+
+// In host code the array's name is only a handle for the runtime, not an address a kernel may dereference; the
+// device address is looked up once per GPU (with that GPU current) and remembered.
+static std::mutex g_noalloc_mu;
+static void *g_noalloc_scratch_addr[64] = {nullptr};
+
+static int noalloc_scratch_address(void **out) {
+    int dev = -1;
+    EGR_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        set_error("egr_bvh_build_noalloc: unsupported device ordinal %d", dev);
+        return EGR_EINVAL;
+    }
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_scratch_addr[dev]) {
+        void *ptr = nullptr;
+        EGR_CUDA_TRY(cudaGetSymbolAddress((void **)&ptr, g_noalloc_build_scratch));
+        g_noalloc_scratch_addr[dev] = ptr;
+    }
+    *out = g_noalloc_scratch_addr[dev];
+    return EGR_OK;
+}
+
+extern "C" int egr_bvh_build_noalloc(const EgrGaussians *g, const EgrConfig *cfg, void *storage, size_t storage_bytes,
+                                     void *stream) {
+    int rc = check_gaussians(g);
+    if (rc) return rc;
+    if (g->count > EGR_NOALLOC_MAX_GAUSSIANS) {
+        set_error("egr_bvh_build_noalloc: %u Gaussians exceed the built-in scratch (limit %u); use egr_bvh_build "
+                  "with caller-provided scratch", g->count, (unsigned)EGR_NOALLOC_MAX_GAUSSIANS);
+        return EGR_EINVAL;
+    }
+    void *scratch = nullptr;
+    rc = noalloc_scratch_address(&scratch);
+    if (rc) return rc;
+    const size_t need = build_scratch_layout(g->count).total;
+    if (need > kNoAllocScratchBytes) {
+        set_error("egr_bvh_build_noalloc: built-in scratch too small (%zu > %zu bytes)", need, kNoAllocScratchBytes);
+        return EGR_ENOMEM;
+    }
+    // Nothing in the scratch has to start at zero: every word the build reads (keys, ids, topology arrays, the
+    // sort's histograms) is written earlier in the same call, so contents left by the previous call are harmless.
+    return egr_bvh_build(g, cfg, storage, storage_bytes, scratch, kNoAllocScratchBytes, stream);
 }

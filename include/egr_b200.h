@@ -157,6 +157,23 @@ int egr_bvh_build(const EgrGaussians *g, const EgrConfig *cfg, void *storage, si
  * bvh_wrapper.cu:33-70) without its three host syncs. */
 int egr_bvh_refit(const EgrGaussians *g, const EgrConfig *cfg, void *storage, size_t storage_bytes, void *stream);
 
+/* No counterpart in the reference (its rebuild calls cudaFree + cudaMalloc three times, bvh_wrapper.h:24-30).
+ * Same result as egr_bvh_build, for hosts that must not allocate device memory when a rebuild is due: e.g. an
+ * application that has handed the whole GPU to its own memory pool (a raw allocation then fails, or forces the
+ * pool to flush and synchronise), or an interactive edit -> re-render loop where the driver-wide lock and implicit
+ * synchronisation of an allocation would show up as a hitch.  The build scratch is a 6 MiB block inside the
+ * library image instead of a caller buffer, which caps the size at EGR_NOALLOC_MAX_GAUSSIANS; larger counts are
+ * rejected with EGR_EINVAL and a message.  The caller still passes the parameters and the BVH storage.
+ *  - The first call on each GPU looks up the block's device address (with that GPU current); make that first call
+ *    outside any stream capture.
+ *  - All calls on a GPU share the one block (it simply keeps whatever the previous call left; nothing in it needs
+ *    clearing).  Two builds that overlap on the same GPU (different streams or threads) would corrupt each other:
+ *    serialise them.
+ *  - Allocates nothing, directly or through a library. */
+#define EGR_NOALLOC_MAX_GAUSSIANS 65536u
+int egr_bvh_build_noalloc(const EgrGaussians *g, const EgrConfig *cfg, void *storage, size_t storage_bytes,
+                          void *stream);
+
 /* ---- tracer (replaces Raytracer::raytrace, csrc/raytracer.cpp:81-94, and the OptiX launch of
  *      __raygen__rg / __intersection__gaussian, csrc/shaders.cu:9-173) -------------------------------- */
 size_t egr_pixel_state_bytes(uint32_t width, uint32_t height, uint32_t num_steps);
