@@ -345,7 +345,7 @@ def run_ours(args):
                        "all-reduce of the flat [N,24] gradient record" if world > 1 else "single GPU",
                        "l2": "inputs larger than L2: >400 MB of records/nodes/params/state/hit log touched per step, "
                              "a different view every step", "hitlog_overflow": overflow},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": (2 + 1 + S + 2) * K,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": (1 + 2 + S + (S - 1) + S + 1) * K,  # refit, pack+begin, S steps, S-1 scans, S backward, end
             "roofline": roofline, "cpu_baseline": cpu, "rays_per_step": rays / K / world,
         }
         print(json.dumps(line))

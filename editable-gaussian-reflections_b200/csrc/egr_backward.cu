@@ -48,16 +48,16 @@ __device__ __forceinline__ void flush_grads(float *grad_records, uint32_t id, bo
     }
 }
 
-__global__ void __launch_bounds__(128) k_backward(const TraceCtx c) {
+__global__ void __launch_bounds__(128) k_backward(const TraceCtx c, const int step) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31;
     if (warp >= c.num_warps) return;
     const EgrConfig &cfg = c.p.config;
     const int B = min(*cfg.num_bounces, (int)c.S - 1);
-    const uint32_t W = c.p.image_width, H = c.p.image_height;
-    const uint32_t px = (warp % c.tiles_x) * 8 + (lane & 7), py = (warp / c.tiles_x) * 4 + (lane >> 3);
-    const bool valid = px < W && py < H;
-    const uint32_t pix = valid ? py * W + px : 0;
+    if (step > B) return;
+    if (step > 0 && warp * 32 >= c.ray_count[step]) return;
+    uint32_t pix = 0;
+    const bool valid = lane_pixel(c, step, warp, lane, pix);  // same lane <-> ray mapping as the forward of `step`
     const int nexec = valid ? (int)(c.steps_executed[pix] & 0xFFu) : 0;  // total_effective_steps
     const float exp_power = *cfg.exp_power;
     const float eps_scale_grad = *cfg.eps_scale_grad;
@@ -77,11 +77,11 @@ __global__ void __launch_bounds__(128) k_backward(const TraceCtx c) {
             if (j < nexec) spec = spec + plane3(c, SP_RGB, j, pix);
     }
 
-    for (int step = min(B, (int)c.S - 1); step >= 0; --step) {  // shaders.cu:157
+    {  // one launch per step, last step first (shaders.cu:157)
         const uint32_t *wt_ = c.warp_tail + ((size_t)warp * c.S + step) * 2;
         uint32_t chunk = wt_[0];
         const int nb = (int)wt_[1];
-        if (nb == 0 || chunk == 0xFFFFFFFFu) continue;
+        if (nb == 0 || chunk == 0xFFFFFFFFu) return;
         const int nh = (valid && step < nexec) ? __float_as_int(plane(c, SP_NHITS, step, pix)) : 0;
         const bool on = nh > 0;
         // per-pixel upstream gradients (backward_pass.cu:81-108)
@@ -235,9 +235,9 @@ k_hitlog_export(const TraceCtx c, const int step, const int cap, int32_t *ids, f
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31;
     if (warp >= c.num_warps) return;
-    const uint32_t px = (warp % c.tiles_x) * 8 + (lane & 7), py = (warp / c.tiles_x) * 4 + (lane >> 3);
-    const bool valid = px < c.p.image_width && py < c.p.image_height;
-    const uint32_t pix = valid ? py * c.p.image_width + px : 0;
+    if (step > 0 && warp * 32 >= c.ray_count[step]) return;
+    uint32_t pix = 0;
+    const bool valid = lane_pixel(c, step, warp, lane, pix);
     const int nexec = valid ? (int)(c.steps_executed[pix] & 0xFFu) : 0;
     const uint32_t *wt_ = c.warp_tail + ((size_t)warp * c.S + step) * 2;
     uint32_t chunk = wt_[0];
@@ -270,7 +270,7 @@ int launch_hitlog_export(const TraceCtx &c, int step, int cap, int32_t *ids, flo
 
 int launch_backward_impl(const TraceCtx &c, cudaStream_t st) {
     const uint32_t blocks = (c.num_warps + 3) / 4;
-    k_backward<<<blocks, 128, 0, st>>>(c);
+    for (int step = (int)c.S - 1; step >= 0; --step) k_backward<<<blocks, 128, 0, st>>>(c, step);
     EGR_CUDA_TRY(cudaGetLastError());
     return EGR_OK;
 }

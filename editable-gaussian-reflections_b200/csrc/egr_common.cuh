@@ -104,7 +104,7 @@ enum StatePlane {
     SP_COUNT = 40
 };
 struct StateLayout {
-    size_t planes, steps_executed, warp_tail, total;
+    size_t planes, steps_executed, warp_tail, ray_pix, warp_mask, warp_off, ray_count, total;
     uint32_t P, S, num_warps;
 };
 __host__ __device__ inline uint32_t tiles_x(uint32_t w) { return (w + 7) / 8; }
@@ -117,6 +117,13 @@ __host__ __device__ inline StateLayout state_layout(uint32_t w, uint32_t h, uint
     L.planes = o, o = align_up(o + (size_t)SP_COUNT * S * L.P * 4, 256);
     L.steps_executed = o, o = align_up(o + (size_t)L.P * 4, 256);
     L.warp_tail = o, o = align_up(o + (size_t)L.num_warps * S * 8, 256);  // (tail chunk, num batches) per warp-step
+    // bounce rays are compacted into dense warps: ray_pix[s][r] = pixel of the r-th ray of step s (s >= 1);
+    // warp_mask[s][w] = lanes of warp w of step s that spawned a ray; warp_off[s] = exclusive scan of the popcounts
+    // of warp_mask[s-1]; ray_count[s] = number of rays of step s
+    L.ray_pix = o, o = align_up(o + (size_t)L.P * S * 4, 256);
+    L.warp_mask = o, o = align_up(o + (size_t)L.num_warps * S * 4, 256);
+    L.warp_off = o, o = align_up(o + (size_t)L.num_warps * S * 4, 256);
+    L.ray_count = o, o = align_up(o + (size_t)S * 4, 256);
     L.total = o;
     return L;
 }

@@ -7,6 +7,7 @@
 // Reference: editable_gauss_refl/cuda/csrc/shaders.cu:9-173, forward_pass.cu:3-156, core/camera.h:17-36,
 // core/framebuffer.h:104-143, utils/ggx_brdf.h:32-37,63,83,134-168, raytracer.cpp:81-94.
 #include <float.h>
+#include <stdlib.h>
 
 #include "egr_trace.cuh"
 
@@ -15,25 +16,24 @@ namespace egr {
 int launch_pack_appearance(const BvhView &bvh, const EgrGaussians &g, cudaStream_t st);
 
 // ---- k-buffer: 16 (t, leaf) pairs sorted ascending by (t, leaf), in registers --------------------------------
-__device__ __forceinline__ bool kless(float t, uint32_t j, float t2, uint32_t j2) {
-    return t < t2 || (t == t2 && j < j2);
-}
+// The walk visits leaves in ascending leaf index in every pass, so a strict `t <` comparison (a newcomer goes behind
+// entries of equal t, and a newcomer equal to the current 16th is refused) yields exactly the (t, leaf) order.
 __device__ __forceinline__ void kb_reset(float (&kt)[KBUF], uint32_t (&kj)[KBUF]) {
 #pragma unroll
     for (int i = 0; i < KBUF; ++i) kt[i] = FLT_MAX, kj[i] = 0xFFFFFFFFu;
 }
-// precondition: kless(t, j, kt[15], kj[15])
+// precondition: t < kt[15]
 __device__ __forceinline__ void kb_insert(float (&kt)[KBUF], uint32_t (&kj)[KBUF], float t, uint32_t j) {
     bool lt[KBUF];
 #pragma unroll
-    for (int i = 0; i < KBUF; ++i) lt[i] = kless(t, j, kt[i], kj[i]);
+    for (int i = 0; i < KBUF; ++i) lt[i] = t < kt[i];
 #pragma unroll
     for (int i = KBUF - 1; i >= 1; --i) {
-        kt[i] = lt[i - 1] ? kt[i - 1] : (lt[i] ? t : kt[i]);
         kj[i] = lt[i - 1] ? kj[i - 1] : (lt[i] ? j : kj[i]);
+        kt[i] = fminf(fmaxf(kt[i - 1], t), kt[i]);
     }
-    kt[0] = lt[0] ? t : kt[0];
     kj[0] = lt[0] ? j : kj[0];
+    kt[0] = fminf(t, kt[0]);
 }
 
 struct StepCfg {
@@ -91,11 +91,76 @@ __device__ __forceinline__ void traverse(
                         T_full = (float)((double)T_full * (1.0 - (double)h.alpha));  // shaders.cu:69-71
                         n_acc++;
                     }
-                    if (h.t > w && kless(h.t, leaf, kt[KBUF - 1], kj[KBUF - 1])) kb_insert(kt, kj, h.t, leaf);
+                    if (h.t > w && h.t < kt[KBUF - 1]) kb_insert(kt, kj, h.t, leaf);
                 }
             }
         }
         node = node + 1;
+    }
+}
+
+// Per-lane stackless walk for incoherent rays (bounce steps): every lane follows its own node index through the
+// same preorder layout ("while-while": each lane runs to its next candidate leaf, then the warp processes the
+// leaves together).  The union walk above would make every lane test every node any lane needs, which is 32x
+// redundant once the rays of a warp fan out.
+template <bool PASS0>
+__device__ __forceinline__ void traverse_lane(
+    const BvhView &bvh, const StepCfg &sc, const f3 o, const f3 d, const f3 idir, const bool active, const float w,
+    float (&kt)[KBUF], uint32_t (&kj)[KBUF], float &T_full, int &n_acc, int &n_trav) {
+    const uint32_t end = bvh.num_nodes;
+    const float4 *__restrict__ nodes = bvh.nodes;
+    uint32_t node = active ? 0u : end;
+    while (true) {
+        uint32_t leaf = INTERNAL;
+        while (node < end) {
+            const float4 A = __ldg(&nodes[2 * (size_t)node]);
+            const float4 B = __ldg(&nodes[2 * (size_t)node + 1]);
+            bool hit = false;
+            if (A.x <= B.x) {
+                float t0x = (A.x - o.x) * idir.x, t1x = (B.x - o.x) * idir.x;
+                float t0y = (A.y - o.y) * idir.y, t1y = (B.y - o.y) * idir.y;
+                float t0z = (A.z - o.z) * idir.z, t1z = (B.z - o.z) * idir.z;
+                float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
+                float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+                tn = tn - fabsf(tn) * 4.0e-7f;
+                tf = tf + fabsf(tf) * 4.0e-7f;
+                float lo = PASS0 ? sc.tmin : fmaxf(sc.tmin, w);
+                float hi = PASS0 ? sc.tmax : fminf(sc.tmax, kt[KBUF - 1]);
+                hit = fmaxf(tn, lo) <= fminf(tf, hi);
+            }
+            if (!hit) {
+                node = __float_as_uint(A.w);
+                continue;
+            }
+            node = node + 1;
+            const uint32_t lf = __float_as_uint(B.w);
+            if (lf != INTERNAL) {
+                leaf = lf;
+                break;
+            }
+        }
+        if (!__any_sync(0xffffffffu, leaf != INTERNAL)) break;
+        if (leaf != INTERNAL) {
+            const float4 r0 = __ldg(&bvh.records[4 * (size_t)leaf + 0]);
+            const float4 r1 = __ldg(&bvh.records[4 * (size_t)leaf + 1]);
+            const float4 r2 = __ldg(&bvh.records[4 * (size_t)leaf + 2]);
+            const float4 r3 = __ldg(&bvh.records[4 * (size_t)leaf + 3]);
+            n_trav++;
+            HitEval h;
+            bool ok = eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);
+            if (ok && sc.step != 0 && h.t < sc.bf_dist) {  // shaders.cu:53-61
+                const float4 nq = __ldg(&bvh.appearance[3 * (size_t)leaf + 1]);
+                f3 nrm = mk3(nq.x, nq.y, nq.z);
+                if (sqrtf(dot3(nrm, nrm)) > sc.bf_thr && dot3(nrm, h.dh) > 0.0f) ok = false;
+            }
+            if (ok) {
+                if (PASS0) {
+                    T_full = (float)((double)T_full * (1.0 - (double)h.alpha));  // shaders.cu:69-71
+                    n_acc++;
+                }
+                if (h.t > w && h.t < kt[KBUF - 1]) kb_insert(kt, kj, h.t, leaf);
+            }
+        }
     }
 }
 
@@ -121,7 +186,36 @@ __global__ void __launch_bounds__(256) k_begin(TraceCtx c, int grads) {
     for (uint32_t k = i; k < nt; k += gridDim.x * blockDim.x) {
         c.warp_tail[2 * (size_t)k] = 0xFFFFFFFFu;
         c.warp_tail[2 * (size_t)k + 1] = 0u;
+        c.warp_mask[k] = 0u;
     }
+    if (i < c.S) c.ray_count[i] = i == 0 ? c.P : 0u;
+}
+
+// Exclusive scan of the spawn counts of step-1's warps -> offsets of their rays in the compacted list of `step`.
+// One block; the list keeps tile order (a row of neighbouring 8x4 tiles feeds consecutive dense warps), which is
+// what keeps bounce rays of one warp coherent, and makes the ray order deterministic.
+__global__ void __launch_bounds__(1024) k_scan_spawned(const TraceCtx c, const int step) {
+    __shared__ uint32_t s_part[1024];
+    const uint32_t *mask = c.warp_mask + (size_t)(step - 1) * c.num_warps;
+    uint32_t *off = c.warp_off + (size_t)step * c.num_warps;
+    const uint32_t n = c.num_warps, t = threadIdx.x;
+    const uint32_t per = (n + 1023) / 1024, lo = min(t * per, n), hi = min(lo + per, n);
+    uint32_t sum = 0;
+    for (uint32_t k = lo; k < hi; ++k) sum += __popc(mask[k]);
+    s_part[t] = sum;
+    __syncthreads();
+    for (uint32_t d = 1; d < 1024; d <<= 1) {
+        uint32_t v = t >= d ? s_part[t - d] : 0;
+        __syncthreads();
+        s_part[t] += v;
+        __syncthreads();
+    }
+    uint32_t run = s_part[t] - sum;
+    for (uint32_t k = lo; k < hi; ++k) {
+        off[k] = run;
+        run += __popc(mask[k]);
+    }
+    if (t == 1023) c.ray_count[step] = s_part[1023];
 }
 __global__ void k_end(TraceCtx c) {  // raytracer.cpp:91-93 without the host sync
     if (threadIdx.x == 0 && blockIdx.x == 0 && *c.p.config.accumulate_samples)
@@ -130,22 +224,23 @@ __global__ void k_end(TraceCtx c) {  // raytracer.cpp:91-93 without the host syn
 
 // ---- one ray-step for every pixel ----------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int step, const int grads) {
+    __shared__ float s_kt[4][KBUF * 32];
+    __shared__ uint32_t s_kj[4][KBUF * 32];
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     if (warp >= c.num_warps) return;
     const EgrConfig &cfg = c.p.config;
     const int B = min(*cfg.num_bounces, (int)c.S - 1);  // shaders.cu:85
     if (step > B) return;
     const uint32_t W = c.p.image_width, H = c.p.image_height;
-    const uint32_t px = (warp % c.tiles_x) * 8 + (lane & 7), py = (warp / c.tiles_x) * 4 + (lane >> 3);
-    const bool valid = px < W && py < H;
-    const uint32_t pix = valid ? py * W + px : 0;
 
     bool alive;
+    uint32_t pix = 0;
     f3 o, d;
     uint32_t seed = 0;
     if (step == 0) {
-        alive = valid;
+        alive = lane_pixel(c, 0, warp, lane, pix);
+        const uint32_t px = pix % W, py = pix / W;
         seed = tea4(pix, *c.p.metadata.total_num_calls);  // shaders.cu:88
         // camera.h:17-36
         float view_size = tanf(*c.p.camera.vertical_fov_radians / 2);
@@ -163,13 +258,28 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
         o = mk3(c.p.camera.origin[0], c.p.camera.origin[1], c.p.camera.origin[2]);
         d = normalize3(w0 * x + w1 * y - w2);
     } else {
-        alive = valid && c.steps_executed[pix] == ((uint32_t)step | 0x100u);
+        // dense warps over the compacted list of rays spawned by the previous step
+        const uint32_t cnt = c.ray_count[step];
+        if (warp * 32 >= cnt) return;
+        const uint32_t r = warp * 32 + lane;
+        alive = r < cnt;
+        o = mk3(0, 0, 0), d = mk3(0, 0, 1);
         if (alive) {
+            const uint32_t *off = c.warp_off + (size_t)step * c.num_warps;
+            uint32_t lo = 0, hi = c.num_warps;  // last source warp whose offset is <= r
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (off[mid] <= r) lo = mid; else hi = mid;
+            }
+            uint32_t m = c.warp_mask[(size_t)(step - 1) * c.num_warps + lo];
+            for (uint32_t k = r - off[lo]; k > 0; --k) m &= m - 1;
+            const uint32_t bit = __ffs(m) - 1;
+            if (step == 1) lane_pixel(c, 0, lo, bit, pix);
+            else pix = c.ray_pix[(size_t)(step - 1) * c.P + lo * 32 + bit];
+            c.ray_pix[(size_t)step * c.P + r] = pix;
             o = plane3(c, SP_NEXT_O, step - 1, pix);
             d = plane3(c, SP_NEXT_D, step - 1, pix);
             seed = c.p.metadata.random_seeds[pix];
-        } else {
-            o = mk3(0, 0, 0), d = mk3(0, 0, 1);
         }
     }
     if (!__any_sync(0xffffffffu, alive)) return;
@@ -193,8 +303,11 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
     float w = sc.tmin;
     bool done = !alive;
 
+    // primary rays of an 8x4 tile are coherent: one warp-uniform walk; bounce rays fan out: per-lane walks
+    const bool lane_walk = c.force_walk == 2 || (c.force_walk == 0 && step > 0);
     kb_reset(kt, kj);
-    traverse<true>(c.bvh, sc, o, d, idir, alive, w, kt, kj, T_full, n_acc, n_trav);
+    if (lane_walk) traverse_lane<true>(c.bvh, sc, o, d, idir, alive, w, kt, kj, T_full, n_acc, n_trav);
+    else traverse<true>(c.bvh, sc, o, d, idir, alive, w, kt, kj, T_full, n_acc, n_trav);
 
     uint32_t tail_chunk = 0xFFFFFFFFu, nbatches = 0;
     bool log_ok = grads != 0;
@@ -220,37 +333,38 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
                 nbatches++;
             }
         }
-        if (!done) {
+        // the batch goes through shared memory so that the composite loop can index it dynamically (small code)
 #pragma unroll
-            for (int i = 0; i < KBUF; ++i) {
-                const float t = kt[i];
-                if (!done) {
-                    w = fmaxf(w, t);  // forward_pass.cu:89
-                    if (t < sc.tmax) {
-                        const uint32_t j = kj[i];
-                        const float4 r0 = __ldg(&c.bvh.records[4 * (size_t)j + 0]);
-                        const float4 r1 = __ldg(&c.bvh.records[4 * (size_t)j + 1]);
-                        const float4 r2 = __ldg(&c.bvh.records[4 * (size_t)j + 2]);
-                        const float4 r3 = __ldg(&c.bvh.records[4 * (size_t)j + 3]);
-                        HitEval h;
-                        eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);  // same bits as in the walk
-                        const float4 a0 = __ldg(&c.bvh.appearance[3 * (size_t)j + 0]);
-                        const float4 a1 = __ldg(&c.bvh.appearance[3 * (size_t)j + 1]);
-                        const float4 a2 = __ldg(&c.bvh.appearance[3 * (size_t)j + 2]);
-                        const float nextT = T * (1.0f - h.alpha);  // forward_pass.cu:108-115
-                        const float wt = T - nextT;
-                        c_rgb = c_rgb + mk3(a0.x, a0.y, a0.z) * wt;
-                        c_n = c_n + mk3(a1.x, a1.y, a1.z) * wt;
-                        c_f0 = c_f0 + mk3(a2.x, a2.y, a2.z) * wt;
-                        c_rough += a0.w * wt;
-                        c_depth += t * wt;
-                        T = nextT;
-                        if (chunk) chunk[i * 32 + lane] = make_float4(__uint_as_float(j), t, h.alpha, T);
-                        nh++;
-                        if (T < T_thr) {  // forward_pass.cu:131-134
-                            w = sc.tmax;
-                            done = true;
-                        }
+        for (int i = 0; i < KBUF; ++i) s_kt[wib][i * 32 + lane] = kt[i], s_kj[wib][i * 32 + lane] = kj[i];
+        for (int i = 0; i < KBUF; ++i) {
+            if (!__any_sync(0xffffffffu, !done)) break;
+            if (!done) {
+                const float t = s_kt[wib][i * 32 + lane];
+                w = fmaxf(w, t);  // forward_pass.cu:89
+                if (t < sc.tmax) {
+                    const uint32_t j = s_kj[wib][i * 32 + lane];
+                    const float4 r0 = __ldg(&c.bvh.records[4 * (size_t)j + 0]);
+                    const float4 r1 = __ldg(&c.bvh.records[4 * (size_t)j + 1]);
+                    const float4 r2 = __ldg(&c.bvh.records[4 * (size_t)j + 2]);
+                    const float4 r3 = __ldg(&c.bvh.records[4 * (size_t)j + 3]);
+                    HitEval h;
+                    eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);  // same bits as in the walk
+                    const float4 a0 = __ldg(&c.bvh.appearance[3 * (size_t)j + 0]);
+                    const float4 a1 = __ldg(&c.bvh.appearance[3 * (size_t)j + 1]);
+                    const float4 a2 = __ldg(&c.bvh.appearance[3 * (size_t)j + 2]);
+                    const float nextT = T * (1.0f - h.alpha);  // forward_pass.cu:108-115
+                    const float wt = T - nextT;
+                    c_rgb = c_rgb + mk3(a0.x, a0.y, a0.z) * wt;
+                    c_n = c_n + mk3(a1.x, a1.y, a1.z) * wt;
+                    c_f0 = c_f0 + mk3(a2.x, a2.y, a2.z) * wt;
+                    c_rough += a0.w * wt;
+                    c_depth += t * wt;
+                    T = nextT;
+                    if (chunk) chunk[i * 32 + lane] = make_float4(__uint_as_float(j), t, h.alpha, T);
+                    nh++;
+                    if (T < T_thr) {  // forward_pass.cu:131-134
+                        w = sc.tmax;
+                        done = true;
                     }
                 }
             }
@@ -261,7 +375,8 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
         kb_reset(kt, kj);
         int dummy_acc = 0;
         float dummy_T = 1.0f;
-        traverse<false>(c.bvh, sc, o, d, idir, !done, w, kt, kj, dummy_T, dummy_acc, n_trav);
+        if (lane_walk) traverse_lane<false>(c.bvh, sc, o, d, idir, !done, w, kt, kj, dummy_T, dummy_acc, n_trav);
+        else traverse<false>(c.bvh, sc, o, d, idir, !done, w, kt, kj, dummy_T, dummy_acc, n_trav);
     }
 
     if (lane == 0) {
@@ -269,107 +384,112 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
         wt_[0] = log_ok ? tail_chunk : 0xFFFFFFFFu;
         wt_[1] = log_ok ? nbatches : 0u;
     }
-    if (!alive) return;
+    bool spawned = false;
+    if (alive) {
+        // ---- remaining fill (forward_pass.cu:143-155)
+        const float rem_T = T - T_full;
+        const float nrm = fmaxf(1.0f - T, *cfg.eps_forward_normalization);
+        f3 rem_rgb = div_s(c_rgb, nrm);
+        f3 o_rgb = c_rgb + rem_T * rem_rgb;
+        float rem_depth = c_depth / nrm;
+        float o_depth = c_depth + rem_T * rem_depth;
+        f3 rem_n = div_s(c_n, nrm);
+        f3 o_n = c_n + rem_T * rem_n;
+        f3 rem_f0 = div_s(c_f0, nrm);
+        f3 o_f0 = c_f0 + rem_T * rem_f0;
+        float rem_rough = c_rough / nrm;
+        float o_rough = c_rough + rem_T * rem_rough;
 
-    // ---- remaining fill (forward_pass.cu:143-155)
-    const float rem_T = T - T_full;
-    const float nrm = fmaxf(1.0f - T, *cfg.eps_forward_normalization);
-    f3 rem_rgb = div_s(c_rgb, nrm);
-    f3 o_rgb = c_rgb + rem_T * rem_rgb;
-    float rem_depth = c_depth / nrm;
-    float o_depth = c_depth + rem_T * rem_depth;
-    f3 rem_n = div_s(c_n, nrm);
-    f3 o_n = c_n + rem_T * rem_n;
-    f3 rem_f0 = div_s(c_f0, nrm);
-    f3 o_f0 = c_f0 + rem_T * rem_f0;
-    float rem_rough = c_rough / nrm;
-    float o_rough = c_rough + rem_T * rem_rough;
-
-    f3 thr_prev = mk3(1, 1, 1);
-    if (step > 0) {  // shaders.cu:112-114
-        thr_prev = plane3(c, SP_THR, step - 1, pix);
-        o_rgb = o_rgb * thr_prev;
-    }
-    set_plane3(c, SP_RGB, step, pix, o_rgb);
-    plane(c, SP_DEPTH, step, pix) = o_depth;
-    set_plane3(c, SP_NORMAL, step, pix, o_n);
-    set_plane3(c, SP_F0, step, pix, o_f0);
-    plane(c, SP_ROUGH, step, pix) = o_rough;
-    plane(c, SP_T, step, pix) = T;
-    plane(c, SP_TFULL, step, pix) = T_full;
-    if (grads) {
-        set_plane3(c, SP_REM_RGB, step, pix, rem_rgb);
-        plane(c, SP_REM_DEPTH, step, pix) = rem_depth;
-        set_plane3(c, SP_REM_NORMAL, step, pix, rem_n);
-        set_plane3(c, SP_REM_F0, step, pix, rem_f0);
-        plane(c, SP_REM_ROUGH, step, pix) = rem_rough;
-        set_plane3(c, SP_RAY_O, step, pix, o);
-        set_plane3(c, SP_RAY_D, step, pix, d);
-    }
-    plane(c, SP_NHITS, step, pix) = __int_as_float(log_ok || !grads ? nh : 0);
-    if (c.p.used_ray_origin) st3(c.p.used_ray_origin, (size_t)step * c.P + pix, o);
-    if (c.p.used_ray_direction) st3(c.p.used_ray_direction, (size_t)step * c.P + pix, d);
-    if (c.p.step_executed) c.p.step_executed[(size_t)step * c.P + pix] = 1;
-
-    c.p.stats.num_traversed_per_pixel[pix] += n_trav;
-    c.p.stats.num_hits_per_pixel[pix] += n_acc;
-    c.p.stats.num_composited_per_pixel[pix] += nh;
-    c.p.stats.num_steps_per_pixel[pix] += 1;
-    c.p.stats.num_accumulated_per_pixel[pix] = nh;  // forward_pass.cu:140 (last executed step wins)
-
-    // ---- bounce (shaders.cu:116-146)
-    uint32_t exec_code = (uint32_t)(step + 1);
-    f3 thr = mk3(1, 1, 1), next_o = mk3(0, 0, 0), next_d = mk3(0, 0, 0);
-    const f3 un = o_n;
-    if (!(length3(un) < *cfg.reflection_invalid_normal_threshold)) {
-        const f3 en = normalize3(un);
-        const float er = fmaxf(o_rough, *cfg.eps_min_roughness);
-        const f3 epos = o + o_depth * d;
-        const float u1 = rnd01(seed);
-        const float u2 = rnd01(seed);
-        const f3 V = -d;
-        // sample_cook_torrance (ggx_brdf.h:152-168)
-        const float a = er * er;
-        const float phi = (float)(2.0f * 3.14159265358979323846 * (double)u1);
-        const float cosT = sqrtf((1.0f - u2) / (1.0f + (a * a - 1.0f) * u2));
-        const float sinT = sqrtf(fmaf(-cosT, cosT, 1.0f));
-        float sp, cp;
-        sincosf(phi, &sp, &cp);
-        const f3 Hl = mk3(sinT * cp, sinT * sp, cosT);
-        const f3 Tn = normalize3(cross3(en.z < 0.999f ? mk3(0, 0, 1) : mk3(1, 0, 0), en));
-        const f3 Bn = cross3(en, Tn);
-        const f3 Hh = Hl.x * Tn + Hl.y * Bn + Hl.z * en;
-        const f3 inc = -V;
-        next_d = inc - 2.0f * Hh * dotp(Hh, inc);
-        next_o = epos + *cfg.eps_ray_surface_offset * next_d;
-        // cook_torrance_weight (ggx_brdf.h:134-150)
-        f3 wgt = mk3(0, 0, 0);
-        if (!(o_f0.x == 0.0f && o_f0.y == 0.0f && o_f0.z == 0.0f)) {
-            const f3 L = next_d;
-            const f3 Hn = normalize3(V + L);
-            const float NdotH = fmaxf(dotp(en, Hn), 0.0f);
-            const float VdotH = fmaxf(dotp(V, Hn), 0.0f);
-            const float NdotV = fmaxf(dotp(en, V), 0.0f);
-            const float kk = (a * a) / 2.0f;
-            const float NdotL = fmaxf(dotp(en, L), 0.0f);
-            const float g1v = (float)(NdotV / ((double)(NdotV * (1.0f - kk) + kk) + 1e-8));
-            const float g1l = (float)(NdotL / ((double)(NdotL * (1.0f - kk) + kk) + 1e-8));
-            const float G = g1v * g1l;
-            const float pw = 1.0f - VdotH;
-            float p5 = pw * pw;
-            p5 = p5 * p5 * pw;
-            const f3 F = o_f0 + (mk3(1, 1, 1) - o_f0) * p5;
-            const float den = (float)((double)(NdotH * NdotV) + 1e-8);
-            wgt = div_s(F * G * VdotH, den);
+        f3 thr_prev = mk3(1, 1, 1);
+        if (step > 0) {  // shaders.cu:112-114
+            thr_prev = plane3(c, SP_THR, step - 1, pix);
+            o_rgb = o_rgb * thr_prev;
         }
-        thr = thr_prev * wgt;
-        exec_code |= 0x100u;
+        set_plane3(c, SP_RGB, step, pix, o_rgb);
+        plane(c, SP_DEPTH, step, pix) = o_depth;
+        set_plane3(c, SP_NORMAL, step, pix, o_n);
+        set_plane3(c, SP_F0, step, pix, o_f0);
+        plane(c, SP_ROUGH, step, pix) = o_rough;
+        plane(c, SP_T, step, pix) = T;
+        plane(c, SP_TFULL, step, pix) = T_full;
+        if (grads) {
+            set_plane3(c, SP_REM_RGB, step, pix, rem_rgb);
+            plane(c, SP_REM_DEPTH, step, pix) = rem_depth;
+            set_plane3(c, SP_REM_NORMAL, step, pix, rem_n);
+            set_plane3(c, SP_REM_F0, step, pix, rem_f0);
+            plane(c, SP_REM_ROUGH, step, pix) = rem_rough;
+            set_plane3(c, SP_RAY_O, step, pix, o);
+            set_plane3(c, SP_RAY_D, step, pix, d);
+        }
+        plane(c, SP_NHITS, step, pix) = __int_as_float(log_ok || !grads ? nh : 0);
+        if (c.p.used_ray_origin) st3(c.p.used_ray_origin, (size_t)step * c.P + pix, o);
+        if (c.p.used_ray_direction) st3(c.p.used_ray_direction, (size_t)step * c.P + pix, d);
+        if (c.p.step_executed) c.p.step_executed[(size_t)step * c.P + pix] = 1;
+
+        c.p.stats.num_traversed_per_pixel[pix] += n_trav;
+        c.p.stats.num_hits_per_pixel[pix] += n_acc;
+        c.p.stats.num_composited_per_pixel[pix] += nh;
+        c.p.stats.num_steps_per_pixel[pix] += 1;
+        c.p.stats.num_accumulated_per_pixel[pix] = nh;  // forward_pass.cu:140 (last executed step wins)
+
+        // ---- bounce (shaders.cu:116-146)
+        uint32_t exec_code = (uint32_t)(step + 1);
+        f3 thr = mk3(1, 1, 1), next_o = mk3(0, 0, 0), next_d = mk3(0, 0, 0);
+        const f3 un = o_n;
+        if (!(length3(un) < *cfg.reflection_invalid_normal_threshold)) {
+            const f3 en = normalize3(un);
+            const float er = fmaxf(o_rough, *cfg.eps_min_roughness);
+            const f3 epos = o + o_depth * d;
+            const float u1 = rnd01(seed);
+            const float u2 = rnd01(seed);
+            const f3 V = -d;
+            // sample_cook_torrance (ggx_brdf.h:152-168)
+            const float a = er * er;
+            const float phi = (float)(2.0f * 3.14159265358979323846 * (double)u1);
+            const float cosT = sqrtf((1.0f - u2) / (1.0f + (a * a - 1.0f) * u2));
+            const float sinT = sqrtf(fmaf(-cosT, cosT, 1.0f));
+            float sp, cp;
+            sincosf(phi, &sp, &cp);
+            const f3 Hl = mk3(sinT * cp, sinT * sp, cosT);
+            const f3 Tn = normalize3(cross3(en.z < 0.999f ? mk3(0, 0, 1) : mk3(1, 0, 0), en));
+            const f3 Bn = cross3(en, Tn);
+            const f3 Hh = Hl.x * Tn + Hl.y * Bn + Hl.z * en;
+            const f3 inc = -V;
+            next_d = inc - 2.0f * Hh * dotp(Hh, inc);
+            next_o = epos + *cfg.eps_ray_surface_offset * next_d;
+            // cook_torrance_weight (ggx_brdf.h:134-150)
+            f3 wgt = mk3(0, 0, 0);
+            if (!(o_f0.x == 0.0f && o_f0.y == 0.0f && o_f0.z == 0.0f)) {
+                const f3 L = next_d;
+                const f3 Hn = normalize3(V + L);
+                const float NdotH = fmaxf(dotp(en, Hn), 0.0f);
+                const float VdotH = fmaxf(dotp(V, Hn), 0.0f);
+                const float NdotV = fmaxf(dotp(en, V), 0.0f);
+                const float kk = (a * a) / 2.0f;
+                const float NdotL = fmaxf(dotp(en, L), 0.0f);
+                const float g1v = (float)(NdotV / ((double)(NdotV * (1.0f - kk) + kk) + 1e-8));
+                const float g1l = (float)(NdotL / ((double)(NdotL * (1.0f - kk) + kk) + 1e-8));
+                const float G = g1v * g1l;
+                const float pw = 1.0f - VdotH;
+                float p5 = pw * pw;
+                p5 = p5 * p5 * pw;
+                const f3 F = o_f0 + (mk3(1, 1, 1) - o_f0) * p5;
+                const float den = (float)((double)(NdotH * NdotV) + 1e-8);
+                wgt = div_s(F * G * VdotH, den);
+            }
+            thr = thr_prev * wgt;
+            exec_code |= 0x100u;
+        }
+        set_plane3(c, SP_THR, step, pix, thr);
+        set_plane3(c, SP_NEXT_O, step, pix, next_o);
+        set_plane3(c, SP_NEXT_D, step, pix, next_d);
+        c.steps_executed[pix] = exec_code;
+        spawned = (exec_code & 0x100u) != 0;
+        c.p.metadata.random_seeds[pix] = seed;  // shaders.cu:172 (final value after the last executed step)
     }
-    set_plane3(c, SP_THR, step, pix, thr);
-    set_plane3(c, SP_NEXT_O, step, pix, next_o);
-    set_plane3(c, SP_NEXT_D, step, pix, next_d);
-    c.steps_executed[pix] = exec_code;
-    c.p.metadata.random_seeds[pix] = seed;  // shaders.cu:172 (final value after the last executed step)
+    // lanes that spawned a ray feed the compaction of the next step
+    const unsigned smask = __ballot_sync(0xffffffffu, spawned);
+    if (lane == 0) c.warp_mask[(size_t)step * c.num_warps + warp] = smask;
 }
 
 // ---- no-grad epilogue: accumulate + write every plane of every step (shaders.cu:163-169, framebuffer.h:104-143)
@@ -451,7 +571,15 @@ static int make_ctx(const EgrParams *p, TraceCtx &c) {
     c.planes = (float *)(sb + L.planes);
     c.steps_executed = (uint32_t *)(sb + L.steps_executed);
     c.warp_tail = (uint32_t *)(sb + L.warp_tail);
+    c.ray_pix = (uint32_t *)(sb + L.ray_pix);
+    c.warp_mask = (uint32_t *)(sb + L.warp_mask);
+    c.warp_off = (uint32_t *)(sb + L.warp_off);
+    c.ray_count = (uint32_t *)(sb + L.ray_count);
     c.P = L.P, c.S = L.S, c.tiles_x = tiles_x(p->image_width), c.num_warps = L.num_warps;
+    {
+        const char *e = getenv("EGR_FORCE_WALK");  // debugging aid: 1 = warp-uniform walk everywhere, 2 = per-lane
+        c.force_walk = e ? atoi(e) : 0;
+    }
     c.hitlog_chunks = p->hitlog ? (uint32_t)min((size_t)0x7fffffff, p->hitlog_bytes / HITLOG_CHUNK_BYTES) : 0;
     return EGR_OK;
 }
@@ -489,7 +617,10 @@ extern "C" int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32
     }
     const uint32_t blocks = (c.num_warps + 3) / 4;
     for (uint32_t s = 0; s < c.S; ++s)
-        if (phase_mask & EGR_PHASE_STEP(s)) k_trace_step<<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
+        if (phase_mask & EGR_PHASE_STEP(s)) {
+            if (s > 0) k_scan_spawned<<<1, 1024, 0, st>>>(c, (int)s);
+            k_trace_step<<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
+        }
     if (phase_mask & EGR_PHASE_FINISH) {
         if (grads_enabled) {
             rc = launch_backward_impl(c, st);
