@@ -180,7 +180,9 @@ k_preorder(int n, const uint32_t *__restrict__ child_l, const uint32_t *__restri
     uint32_t skip = pre + 2u * nl - 1u;
     uint32_t ppre = direct_parent == NO_PARENT ? NO_PARENT : 2u * first[direct_parent] + (turns - first_turn);
     nodes[2 * (size_t)pre] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(skip));       // empty box until refit
-    nodes[2 * (size_t)pre + 1] = make_float4(-1.0f, -1.0f, -1.0f, __uint_as_float(is_leaf ? idx : INTERNAL));
+    // leaf: leaf index; internal: FIRST_LEAF_FLAG | first leaf of the subtree (its leaves are the contiguous
+    // range [first, first + (skip - pre + 1) / 2) of the Morton order)
+    nodes[2 * (size_t)pre + 1] = make_float4(-1.0f, -1.0f, -1.0f, __uint_as_float(is_leaf ? idx : (FIRST_LEAF_FLAG | a)));
     parents[pre] = ppre;
     flags[pre] = 0;
     if (is_leaf) leaf_node[idx] = pre;
@@ -223,7 +225,9 @@ __global__ void __launch_bounds__(256) k_refit(BvhView bvh, EgrGaussians g, EgrC
     bvh.records[4 * (size_t)j + 0] = rec[0];
     bvh.records[4 * (size_t)j + 1] = rec[1];
     bvh.records[4 * (size_t)j + 2] = rec[2];
-    bvh.records[4 * (size_t)j + 3] = make_float4(sf, sigma, __uint_as_float(id), visible ? 1.0f : 0.0f);
+    // .w: squared radius of the bounding sphere of the proxy ellipsoid (semi-axes S), slightly inflated; 0 = invisible
+    const float rad = fmaxf(S.x, fmaxf(S.y, S.z)) * 1.001f;
+    bvh.records[4 * (size_t)j + 3] = make_float4(sf, sigma, __uint_as_float(id), visible ? rad * rad : 0.0f);
 
     // world box of the image of [-1,1]^3 under M = R diag(S), inflated so that it is strictly conservative w.r.t.
     // the exact local-space test (which alone defines the candidate set)
@@ -263,8 +267,9 @@ __global__ void __launch_bounds__(256) k_refit(BvhView bvh, EgrGaussians g, EgrC
             b = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), 0.0f);
         }
         float4 pa = __ldcg(&bvh.nodes[2 * (size_t)p]);
+        float4 pb = __ldcg(&bvh.nodes[2 * (size_t)p + 1]);
         a.w = pa.w;  // keep skip
-        b.w = __uint_as_float(INTERNAL);
+        b.w = pb.w;  // keep the first-leaf tag
         __stcg(&bvh.nodes[2 * (size_t)p], a);
         __stcg(&bvh.nodes[2 * (size_t)p + 1], b);
         p = bvh.parents[p];

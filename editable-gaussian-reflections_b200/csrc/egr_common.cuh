@@ -24,7 +24,7 @@ constexpr float A_MAX = 0.9999f;            // flags.h:8  MAX_ALPHA
 constexpr int KBUF = 16;                    // flags.h:16 BUFFER_SIZE
 constexpr int MAX_ITERATIONS = 99;          // flags.h:17
 constexpr float ROUGH_DOWNWEIGHT_POW = 3.f; // flags.h:12-13
-constexpr uint32_t INTERNAL = 0xFFFFFFFFu;  // node.leaf value of an internal node
+constexpr uint32_t FIRST_LEAF_FLAG = 0x80000000u;  // node.leaf of an internal node = flag | first leaf of its subtree
 constexpr uint32_t NO_PARENT = 0xFFFFFFFFu;
 
 // ---- storage layouts -------------------------------------------------------------------------------------
@@ -60,7 +60,7 @@ struct BvhView {
     uint32_t *sorted_ids;   // [n] leaf j -> Gaussian id
     float4 *records;        // [n][4] geometry record in leaf order (layout: include/egr_b200.h)
     float4 *appearance;     // [n][3] activated rgb,rough | normal,_ | f0,_
-    float4 *nodes;          // [num_nodes][2]: (bmin.xyz, skip) (bmax.xyz, leaf)
+    float4 *nodes;          // [num_nodes][2]: (bmin.xyz, skip) (bmax.xyz, leaf | FIRST_LEAF_FLAG+first leaf)
     uint32_t *parents;      // [num_nodes] preorder index of the parent
     uint32_t *leaf_node;    // [n] preorder index of leaf j
     uint32_t *flags;        // [num_nodes] refit arrival counters (self-resetting)

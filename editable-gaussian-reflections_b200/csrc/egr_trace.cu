@@ -41,19 +41,53 @@ struct StepCfg {
     int step;
 };
 
-// Warp-uniform stackless walk.  PASS0 visits every node any lane's segment crosses (needed for the exact total
-// transmittance); later passes only the slab (w, kt[15]) of each lane.
+// One candidate Gaussian against one ray: cheap conservative bounding-sphere reject, then the exact test, the
+// exact total transmittance (pass 0) and the k-buffer.
+template <bool PASS0>
+__device__ __forceinline__ void test_candidate(
+    const BvhView &bvh, const StepCfg &sc, const float4 r0, const float4 r1, const float4 r2, const float4 r3,
+    const uint32_t leaf, const f3 o, const f3 d, const float w, float (&kt)[KBUF], uint32_t (&kj)[KBUF], float &T_full,
+    int &n_acc, int &n_trav) {
+    // the accepted hit point lies on the ray and inside the proxy ellipsoid, hence inside its bounding sphere
+    const f3 p = mk3(r0.w, r1.w, r2.w) - o;
+    const f3 cr = cross3(p, d);
+    if (!(dotp(cr, cr) <= r3.w)) return;  // also rejects invisible Gaussians (radius^2 = 0 ... unless dead centre)
+    if (r3.w == 0.0f) return;
+    n_trav++;
+    HitEval h;
+    bool ok = eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);
+    if (ok && sc.step != 0 && h.t < sc.bf_dist) {  // shaders.cu:53-61
+        const float4 nq = __ldg(&bvh.appearance[3 * (size_t)leaf + 1]);
+        f3 nrm = mk3(nq.x, nq.y, nq.z);
+        if (sqrtf(dot3(nrm, nrm)) > sc.bf_thr && dot3(nrm, h.dh) > 0.0f) ok = false;
+    }
+    if (ok) {
+        if (PASS0) {
+            T_full = (float)((double)T_full * (1.0 - (double)h.alpha));  // shaders.cu:69-71
+            n_acc++;
+        }
+        if (h.t > w && h.t < kt[KBUF - 1]) kb_insert(kt, kj, h.t, leaf);
+    }
+}
+
+// Warp-uniform stackless walk for coherent rays (the primary rays of an 8x4 tile): ONE node index per warp, every
+// lane tests its own ray against the node box.  Subtrees of at most FAT leaves are not descended: their Gaussians
+// are a contiguous range of the Morton-ordered records, which the warp stages into shared memory with one coalesced
+// load and then tests one by one from there (no dependent node loads below that level).  PASS0 visits everything
+// any lane's segment crosses (needed for the exact total transmittance); later passes only the slab (w, kt[15]).
+constexpr uint32_t FAT = 16;
 template <bool PASS0>
 __device__ __forceinline__ void traverse(
     const BvhView &bvh, const StepCfg &sc, const f3 o, const f3 d, const f3 idir, const bool active, const float w,
-    float (&kt)[KBUF], uint32_t (&kj)[KBUF], float &T_full, int &n_acc, int &n_trav) {
+    float (&kt)[KBUF], uint32_t (&kj)[KBUF], float &T_full, int &n_acc, int &n_trav, float4 *s_rec) {
     const uint32_t end = bvh.num_nodes;
     const float4 *__restrict__ nodes = bvh.nodes;
+    const uint32_t lane = threadIdx.x & 31;
     uint32_t node = 0;
     while (node < end) {
         const float4 A = __ldg(&nodes[2 * (size_t)node]);
         const float4 B = __ldg(&nodes[2 * (size_t)node + 1]);
-        const uint32_t skip = __float_as_uint(A.w), leaf = __float_as_uint(B.w);
+        const uint32_t skip = __float_as_uint(A.w), tag = __float_as_uint(B.w);
         bool hit = false;
         if (active && A.x <= B.x) {
             float t0x = (A.x - o.x) * idir.x, t1x = (B.x - o.x) * idir.x;
@@ -67,35 +101,25 @@ __device__ __forceinline__ void traverse(
             float hi = PASS0 ? sc.tmax : fminf(sc.tmax, kt[KBUF - 1]);
             hit = fmaxf(tn, lo) <= fminf(tf, hi);
         }
-        const unsigned m = __ballot_sync(0xffffffffu, hit);
-        if (m == 0) {
+        if (!__any_sync(0xffffffffu, hit)) {
             node = skip;
             continue;
         }
-        if (leaf != INTERNAL) {
-            if (hit) {
-                const float4 r0 = __ldg(&bvh.records[4 * (size_t)leaf + 0]);
-                const float4 r1 = __ldg(&bvh.records[4 * (size_t)leaf + 1]);
-                const float4 r2 = __ldg(&bvh.records[4 * (size_t)leaf + 2]);
-                const float4 r3 = __ldg(&bvh.records[4 * (size_t)leaf + 3]);
-                n_trav++;
-                HitEval h;
-                bool ok = eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);
-                if (ok && sc.step != 0 && h.t < sc.bf_dist) {  // shaders.cu:53-61
-                    const float4 nq = __ldg(&bvh.appearance[3 * (size_t)leaf + 1]);
-                    f3 nrm = mk3(nq.x, nq.y, nq.z);
-                    if (sqrtf(dot3(nrm, nrm)) > sc.bf_thr && dot3(nrm, h.dh) > 0.0f) ok = false;
-                }
-                if (ok) {
-                    if (PASS0) {
-                        T_full = (float)((double)T_full * (1.0 - (double)h.alpha));  // shaders.cu:69-71
-                        n_acc++;
-                    }
-                    if (h.t > w && h.t < kt[KBUF - 1]) kb_insert(kt, kj, h.t, leaf);
-                }
-            }
+        const uint32_t nl = (skip - node + 1) >> 1;  // leaves below this node
+        if (nl > FAT) {
+            node = node + 1;
+            continue;
         }
-        node = node + 1;
+        const uint32_t first = tag & ~FIRST_LEAF_FLAG;
+        __syncwarp();
+        for (uint32_t q = lane; q < nl * 4; q += 32) s_rec[q] = __ldg(&bvh.records[4 * (size_t)first + q]);
+        __syncwarp();
+        for (uint32_t k = 0; k < nl; ++k) {
+            if (hit)
+                test_candidate<PASS0>(bvh, sc, s_rec[4 * k], s_rec[4 * k + 1], s_rec[4 * k + 2], s_rec[4 * k + 3],
+                                      first + k, o, d, w, kt, kj, T_full, n_acc, n_trav);
+        }
+        node = skip;
     }
 }
 
@@ -103,6 +127,8 @@ __device__ __forceinline__ void traverse(
 // same preorder layout ("while-while": each lane runs to its next candidate leaf, then the warp processes the
 // leaves together).  The union walk above would make every lane test every node any lane needs, which is 32x
 // redundant once the rays of a warp fan out.
+constexpr uint32_t NO_LEAF = 0xFFFFFFFFu;
+constexpr uint32_t FAT_LANE = 16;
 template <bool PASS0>
 __device__ __forceinline__ void traverse_lane(
     const BvhView &bvh, const StepCfg &sc, const f3 o, const f3 d, const f3 idir, const bool active, const float w,
@@ -111,7 +137,7 @@ __device__ __forceinline__ void traverse_lane(
     const float4 *__restrict__ nodes = bvh.nodes;
     uint32_t node = active ? 0u : end;
     while (true) {
-        uint32_t leaf = INTERNAL;
+        uint32_t leaf = NO_LEAF, leaf_n = 0;
         while (node < end) {
             const float4 A = __ldg(&nodes[2 * (size_t)node]);
             const float4 B = __ldg(&nodes[2 * (size_t)node + 1]);
@@ -132,33 +158,24 @@ __device__ __forceinline__ void traverse_lane(
                 node = __float_as_uint(A.w);
                 continue;
             }
-            node = node + 1;
-            const uint32_t lf = __float_as_uint(B.w);
-            if (lf != INTERNAL) {
-                leaf = lf;
+            const uint32_t skip = __float_as_uint(A.w), tag = __float_as_uint(B.w);
+            const uint32_t nl = (skip - node + 1) >> 1;
+            if (nl <= FAT_LANE) {  // small subtree: test its (contiguous) Gaussians directly instead of descending
+                leaf = tag & ~FIRST_LEAF_FLAG;
+                leaf_n = nl;
+                node = skip;
                 break;
             }
+            node = node + 1;
         }
-        if (!__any_sync(0xffffffffu, leaf != INTERNAL)) break;
-        if (leaf != INTERNAL) {
-            const float4 r0 = __ldg(&bvh.records[4 * (size_t)leaf + 0]);
-            const float4 r1 = __ldg(&bvh.records[4 * (size_t)leaf + 1]);
-            const float4 r2 = __ldg(&bvh.records[4 * (size_t)leaf + 2]);
-            const float4 r3 = __ldg(&bvh.records[4 * (size_t)leaf + 3]);
-            n_trav++;
-            HitEval h;
-            bool ok = eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);
-            if (ok && sc.step != 0 && h.t < sc.bf_dist) {  // shaders.cu:53-61
-                const float4 nq = __ldg(&bvh.appearance[3 * (size_t)leaf + 1]);
-                f3 nrm = mk3(nq.x, nq.y, nq.z);
-                if (sqrtf(dot3(nrm, nrm)) > sc.bf_thr && dot3(nrm, h.dh) > 0.0f) ok = false;
-            }
-            if (ok) {
-                if (PASS0) {
-                    T_full = (float)((double)T_full * (1.0 - (double)h.alpha));  // shaders.cu:69-71
-                    n_acc++;
-                }
-                if (h.t > w && h.t < kt[KBUF - 1]) kb_insert(kt, kj, h.t, leaf);
+        if (!__any_sync(0xffffffffu, leaf != NO_LEAF)) break;
+        if (leaf != NO_LEAF) {
+            for (uint32_t k = 0; k < leaf_n; ++k) {
+                const float4 r0 = __ldg(&bvh.records[4 * (size_t)(leaf + k) + 0]);
+                const float4 r1 = __ldg(&bvh.records[4 * (size_t)(leaf + k) + 1]);
+                const float4 r2 = __ldg(&bvh.records[4 * (size_t)(leaf + k) + 2]);
+                const float4 r3 = __ldg(&bvh.records[4 * (size_t)(leaf + k) + 3]);
+                test_candidate<PASS0>(bvh, sc, r0, r1, r2, r3, leaf + k, o, d, w, kt, kj, T_full, n_acc, n_trav);
             }
         }
     }
@@ -226,6 +243,7 @@ __global__ void k_end(TraceCtx c) {  // raytracer.cpp:91-93 without the host syn
 __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int step, const int grads) {
     __shared__ float s_kt[4][KBUF * 32];
     __shared__ uint32_t s_kj[4][KBUF * 32];
+    __shared__ float4 s_rec[4][FAT * 4];
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     if (warp >= c.num_warps) return;
@@ -307,7 +325,7 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
     const bool lane_walk = c.force_walk == 2 || (c.force_walk == 0 && step > 0);
     kb_reset(kt, kj);
     if (lane_walk) traverse_lane<true>(c.bvh, sc, o, d, idir, alive, w, kt, kj, T_full, n_acc, n_trav);
-    else traverse<true>(c.bvh, sc, o, d, idir, alive, w, kt, kj, T_full, n_acc, n_trav);
+    else traverse<true>(c.bvh, sc, o, d, idir, alive, w, kt, kj, T_full, n_acc, n_trav, s_rec[wib]);
 
     uint32_t tail_chunk = 0xFFFFFFFFu, nbatches = 0;
     bool log_ok = grads != 0;
@@ -376,7 +394,7 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
         int dummy_acc = 0;
         float dummy_T = 1.0f;
         if (lane_walk) traverse_lane<false>(c.bvh, sc, o, d, idir, !done, w, kt, kj, dummy_T, dummy_acc, n_trav);
-        else traverse<false>(c.bvh, sc, o, d, idir, !done, w, kt, kj, dummy_T, dummy_acc, n_trav);
+        else traverse<false>(c.bvh, sc, o, d, idir, !done, w, kt, kj, dummy_T, dummy_acc, n_trav, s_rec[wib]);
     }
 
     if (lane == 0) {

@@ -44,7 +44,7 @@ def _clz64(x: int) -> int:
 
 
 def build(mean: np.ndarray):
-    """Returns dict(sorted_ids [n], skip [2n-1], leaf [2n-1], parents [2n-1], leaf_node [n])."""
+    """Returns dict(sorted_ids [n], skip / leaf / parents / first_leaf [2n-1], leaf_node [n])."""
     keys = morton_keys(mean)
     n = keys.shape[0]
     order = np.argsort(keys, kind="stable").astype(np.uint32)
@@ -62,9 +62,10 @@ def build(mean: np.ndarray):
     leaf = np.full(nn, INTERNAL, np.uint32)
     parents = np.full(nn, NO_PARENT, np.uint32)
     leaf_node = np.zeros(n, np.uint32)
+    first_leaf = np.zeros(nn, np.uint32)
     if n == 1:
         skip[0], leaf[0], leaf_node[0] = 1, 0, 0
-        return dict(sorted_ids=order, skip=skip, leaf=leaf, parents=parents, leaf_node=leaf_node)
+        return dict(sorted_ids=order, skip=skip, leaf=leaf, parents=parents, leaf_node=leaf_node, first_leaf=first_leaf)
     child_l, child_r, first, last = [None] * (n - 1), [None] * (n - 1), [0] * (n - 1), [0] * (n - 1)
     for i in range(n - 1):
         d = 1 if delta(i, i + 1) - delta(i, i - 1) >= 0 else -1
@@ -101,9 +102,10 @@ def build(mean: np.ndarray):
         nxt += 1
         parents[pre] = par
         if is_leaf:
-            leaf[pre], skip[pre], leaf_node[idx] = idx, pre + 1, pre
+            leaf[pre], skip[pre], leaf_node[idx], first_leaf[pre] = idx, pre + 1, pre, idx
         else:
             skip[pre] = pre + 2 * (last[idx] - first[idx] + 1) - 1
+            first_leaf[pre] = first[idx]
             stack.append((child_r[idx], pre))
             stack.append((child_l[idx], pre))
-    return dict(sorted_ids=order, skip=skip, leaf=leaf, parents=parents, leaf_node=leaf_node)
+    return dict(sorted_ids=order, skip=skip, leaf=leaf, parents=parents, leaf_node=leaf_node, first_leaf=first_leaf)

