@@ -103,12 +103,14 @@ enum StatePlane {
     SP_NHITS = 39,   // int bits: composited hits of this step
     SP_COUNT = 40
 };
+constexpr uint32_t MAX_RESIDENT_WARPS = 4096;  // warps of the persistent forward launch that own a hit list
 struct StateLayout {
-    size_t planes, steps_executed, warp_tail, ray_pix, warp_mask, warp_off, ray_count, total;
+    size_t planes, steps_executed, warp_tail, ray_pix, warp_mask, warp_off, ray_count, work_counter, hitlist, total;
     uint32_t P, S, num_warps;
 };
 __host__ __device__ inline uint32_t tiles_x(uint32_t w) { return (w + 7) / 8; }
 __host__ __device__ inline uint32_t tiles_y(uint32_t h) { return (h + 3) / 4; }
+__host__ __device__ inline uint32_t min_u32(uint32_t a, uint32_t b) { return a < b ? a : b; }
 __host__ __device__ inline StateLayout state_layout(uint32_t w, uint32_t h, uint32_t S) {
     StateLayout L;
     L.P = w * h, L.S = S;
@@ -124,6 +126,9 @@ __host__ __device__ inline StateLayout state_layout(uint32_t w, uint32_t h, uint
     L.warp_mask = o, o = align_up(o + (size_t)L.num_warps * S * 4, 256);
     L.warp_off = o, o = align_up(o + (size_t)L.num_warps * S * 4, 256);
     L.ray_count = o, o = align_up(o + (size_t)S * 4, 256);
+    L.work_counter = o, o = align_up(o + (size_t)S * 4, 256);
+    // per-resident-warp hit lists of the forward (64 entries x 32 lanes x 8 B = 16 KiB each)
+    L.hitlist = o, o = align_up(o + (size_t)min_u32(L.num_warps + 3, MAX_RESIDENT_WARPS) * 64 * 32 * 8, 256);
     L.total = o;
     return L;
 }

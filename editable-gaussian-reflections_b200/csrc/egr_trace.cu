@@ -41,18 +41,48 @@ struct StepCfg {
     int step;
 };
 
+// Per-ray hit list of the collection passes: the (up to) LIST_CAP nearest accepted hits beyond the window, as an
+// unordered set in global memory (slot-major, lanes interleaved; a few tens of MB for the whole machine, L2
+// resident).  16-wide batches are selected from it; a BVH walk is repeated only when a ray has consumed all 64 and
+// is still not opaque.  Appending is one 8-byte store; only rays with more than 64 hits pay for replace-the-farthest.
+constexpr uint32_t LIST_CAP = 64;
+struct LaneList {
+    uint2 *base;      // this warp's region
+    uint32_t cnt;     // hits beyond the window seen by the current collection pass (may exceed LIST_CAP)
+    float maxt;       // farthest distance held (valid once cnt >= 1)
+    uint32_t maxslot;
+};
+__device__ __forceinline__ void list_reset(LaneList &L) { L.cnt = 0, L.maxt = -FLT_MAX, L.maxslot = 0; }
+__device__ __forceinline__ void list_add(LaneList &L, const uint32_t lane, const float t, const uint32_t leaf) {
+    if (L.cnt < LIST_CAP) {
+        L.base[L.cnt * 32 + lane] = make_uint2(__float_as_uint(t), leaf);
+        if (t > L.maxt) L.maxt = t, L.maxslot = L.cnt;
+    } else if (t < L.maxt) {  // full: the newcomer replaces the farthest entry, then the new farthest is found
+        L.base[L.maxslot * 32 + lane] = make_uint2(__float_as_uint(t), leaf);
+        float m = -FLT_MAX;
+        uint32_t ms = 0;
+        for (uint32_t e = 0; e < LIST_CAP; ++e) {
+            const float te = __uint_as_float(L.base[e * 32 + lane].x);
+            if (te > m) m = te, ms = e;
+        }
+        L.maxt = m, L.maxslot = ms;
+    }
+    L.cnt++;
+}
+
 // One candidate Gaussian against one ray: cheap conservative bounding-sphere reject, then the exact test, the
-// exact total transmittance (pass 0) and the k-buffer.
+// exact total transmittance (pass 0) and the hit list.
 template <bool PASS0>
 __device__ __forceinline__ void test_candidate(
     const BvhView &bvh, const StepCfg &sc, const float4 r0, const float4 r1, const float4 r2, const float4 r3,
-    const uint32_t leaf, const f3 o, const f3 d, const float w, float (&kt)[KBUF], uint32_t (&kj)[KBUF], float &T_full,
-    int &n_acc, int &n_trav) {
-    // the accepted hit point lies on the ray and inside the proxy ellipsoid, hence inside its bounding sphere
+    const uint32_t leaf, const f3 o, const f3 d, const float w, LaneList &L, float &T_full, int &n_acc, int &n_trav) {
+    // the accepted hit point lies on the forward ray and inside the proxy ellipsoid, hence inside its bounding
+    // sphere: reject when the line misses the sphere, or when the sphere lies wholly behind the origin
     const f3 p = mk3(r0.w, r1.w, r2.w) - o;
     const f3 cr = cross3(p, d);
-    if (!(dotp(cr, cr) <= r3.w)) return;  // also rejects invisible Gaussians (radius^2 = 0 ... unless dead centre)
-    if (r3.w == 0.0f) return;
+    if (!(dotp(cr, cr) <= r3.w)) return;
+    if (r3.w == 0.0f) return;  // invisible Gaussian (radius^2 = 0) that happens to sit exactly on the ray
+    if (dotp(p, d) < 0.0f && dotp(p, p) > r3.w) return;
     n_trav++;
     HitEval h;
     bool ok = eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);
@@ -66,7 +96,7 @@ __device__ __forceinline__ void test_candidate(
             T_full = (float)((double)T_full * (1.0 - (double)h.alpha));  // shaders.cu:69-71
             n_acc++;
         }
-        if (h.t > w && h.t < kt[KBUF - 1]) kb_insert(kt, kj, h.t, leaf);
+        if (h.t > w) list_add(L, threadIdx.x & 31, h.t, leaf);  // strict, as forward_pass.cu:62
     }
 }
 
@@ -74,12 +104,12 @@ __device__ __forceinline__ void test_candidate(
 // lane tests its own ray against the node box.  Subtrees of at most FAT leaves are not descended: their Gaussians
 // are a contiguous range of the Morton-ordered records, which the warp stages into shared memory with one coalesced
 // load and then tests one by one from there (no dependent node loads below that level).  PASS0 visits everything
-// any lane's segment crosses (needed for the exact total transmittance); later passes only the slab (w, kt[15]).
+// any lane's segment crosses (needed for the exact total transmittance); later passes only the slab (w, farthest list entry).
 constexpr uint32_t FAT = 16;
 template <bool PASS0>
 __device__ __forceinline__ void traverse(
     const BvhView &bvh, const StepCfg &sc, const f3 o, const f3 d, const f3 idir, const bool active, const float w,
-    float (&kt)[KBUF], uint32_t (&kj)[KBUF], float &T_full, int &n_acc, int &n_trav, float4 *s_rec) {
+    LaneList &L, float &T_full, int &n_acc, int &n_trav, float4 *s_rec) {
     const uint32_t end = bvh.num_nodes;
     const float4 *__restrict__ nodes = bvh.nodes;
     const uint32_t lane = threadIdx.x & 31;
@@ -98,7 +128,7 @@ __device__ __forceinline__ void traverse(
             tn = tn - fabsf(tn) * 4.0e-7f;
             tf = tf + fabsf(tf) * 4.0e-7f;
             float lo = PASS0 ? sc.tmin : fmaxf(sc.tmin, w);
-            float hi = PASS0 ? sc.tmax : fminf(sc.tmax, kt[KBUF - 1]);
+            float hi = PASS0 || L.cnt < LIST_CAP ? sc.tmax : fminf(sc.tmax, L.maxt);
             hit = fmaxf(tn, lo) <= fminf(tf, hi);
         }
         if (!__any_sync(0xffffffffu, hit)) {
@@ -117,7 +147,7 @@ __device__ __forceinline__ void traverse(
         for (uint32_t k = 0; k < nl; ++k) {
             if (hit)
                 test_candidate<PASS0>(bvh, sc, s_rec[4 * k], s_rec[4 * k + 1], s_rec[4 * k + 2], s_rec[4 * k + 3],
-                                      first + k, o, d, w, kt, kj, T_full, n_acc, n_trav);
+                                      first + k, o, d, w, L, T_full, n_acc, n_trav);
         }
         node = skip;
     }
@@ -132,7 +162,7 @@ constexpr uint32_t FAT_LANE = 16;
 template <bool PASS0>
 __device__ __forceinline__ void traverse_lane(
     const BvhView &bvh, const StepCfg &sc, const f3 o, const f3 d, const f3 idir, const bool active, const float w,
-    float (&kt)[KBUF], uint32_t (&kj)[KBUF], float &T_full, int &n_acc, int &n_trav) {
+    LaneList &L, float &T_full, int &n_acc, int &n_trav) {
     const uint32_t end = bvh.num_nodes;
     const float4 *__restrict__ nodes = bvh.nodes;
     uint32_t node = active ? 0u : end;
@@ -151,7 +181,7 @@ __device__ __forceinline__ void traverse_lane(
                 tn = tn - fabsf(tn) * 4.0e-7f;
                 tf = tf + fabsf(tf) * 4.0e-7f;
                 float lo = PASS0 ? sc.tmin : fmaxf(sc.tmin, w);
-                float hi = PASS0 ? sc.tmax : fminf(sc.tmax, kt[KBUF - 1]);
+                float hi = PASS0 || L.cnt < LIST_CAP ? sc.tmax : fminf(sc.tmax, L.maxt);
                 hit = fmaxf(tn, lo) <= fminf(tf, hi);
             }
             if (!hit) {
@@ -175,7 +205,7 @@ __device__ __forceinline__ void traverse_lane(
                 const float4 r1 = __ldg(&bvh.records[4 * (size_t)(leaf + k) + 1]);
                 const float4 r2 = __ldg(&bvh.records[4 * (size_t)(leaf + k) + 2]);
                 const float4 r3 = __ldg(&bvh.records[4 * (size_t)(leaf + k) + 3]);
-                test_candidate<PASS0>(bvh, sc, r0, r1, r2, r3, leaf + k, o, d, w, kt, kj, T_full, n_acc, n_trav);
+                test_candidate<PASS0>(bvh, sc, r0, r1, r2, r3, leaf + k, o, d, w, L, T_full, n_acc, n_trav);
             }
         }
     }
@@ -205,7 +235,7 @@ __global__ void __launch_bounds__(256) k_begin(TraceCtx c, int grads) {
         c.warp_tail[2 * (size_t)k + 1] = 0u;
         c.warp_mask[k] = 0u;
     }
-    if (i < c.S) c.ray_count[i] = i == 0 ? c.P : 0u;
+    if (i < c.S) c.ray_count[i] = i == 0 ? c.P : 0u, c.work_counter[i] = 0u;
 }
 
 // Exclusive scan of the spawn counts of step-1's warps -> offsets of their rays in the compacted list of `step`.
@@ -239,17 +269,11 @@ __global__ void k_end(TraceCtx c) {  // raytracer.cpp:91-93 without the host syn
         *c.p.framebuffer.accumulated_sample_count += 1;
 }
 
-// ---- one ray-step for every pixel ----------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int step, const int grads) {
-    __shared__ float s_kt[4][KBUF * 32];
-    __shared__ uint32_t s_kj[4][KBUF * 32];
-    __shared__ float4 s_rec[4][FAT * 4];
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    if (warp >= c.num_warps) return;
+// ---- one ray-step of one warp's 32 rays ------------------------------------------------------------------------
+__device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, const int grads, const uint32_t warp,
+                                           const uint32_t lane, float *s_kt, uint32_t *s_kj, float4 *s_rec,
+                                           uint2 *list) {
     const EgrConfig &cfg = c.p.config;
-    const int B = min(*cfg.num_bounces, (int)c.S - 1);  // shaders.cu:85
-    if (step > B) return;
     const uint32_t W = c.p.image_width, H = c.p.image_height;
 
     bool alive;
@@ -278,7 +302,6 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
     } else {
         // dense warps over the compacted list of rays spawned by the previous step
         const uint32_t cnt = c.ray_count[step];
-        if (warp * 32 >= cnt) return;
         const uint32_t r = warp * 32 + lane;
         alive = r < cnt;
         o = mk3(0, 0, 0), d = mk3(0, 0, 1);
@@ -314,6 +337,7 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
 
     float kt[KBUF];
     uint32_t kj[KBUF];
+    kb_reset(kt, kj);
     float T_full = 1.0f, T = 1.0f;
     int n_acc = 0, n_trav = 0, nh = 0;
     f3 c_rgb = mk3(0, 0, 0), c_n = mk3(0, 0, 0), c_f0 = mk3(0, 0, 0);
@@ -323,17 +347,47 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
 
     // primary rays of an 8x4 tile are coherent: one warp-uniform walk; bounce rays fan out: per-lane walks
     const bool lane_walk = c.force_walk == 2 || (c.force_walk == 0 && step > 0);
-    kb_reset(kt, kj);
-    if (lane_walk) traverse_lane<true>(c.bvh, sc, o, d, idir, alive, w, kt, kj, T_full, n_acc, n_trav);
-    else traverse<true>(c.bvh, sc, o, d, idir, alive, w, kt, kj, T_full, n_acc, n_trav, s_rec[wib]);
+    LaneList L;
+    L.base = list;
+    list_reset(L);
+    if (lane_walk) traverse_lane<true>(c.bvh, sc, o, d, idir, alive, w, L, T_full, n_acc, n_trav);
+    else traverse<true>(c.bvh, sc, o, d, idir, alive, w, L, T_full, n_acc, n_trav, s_rec);
 
     uint32_t tail_chunk = 0xFFFFFFFFu, nbatches = 0;
     bool log_ok = grads != 0;
     char *hitlog = (char *)c.p.hitlog;
 
+    // select: the 16 nearest list entries beyond the window -> register k-buffer (forward_pass.cu:57-78)
+    auto select_batch = [&](const bool on) {
+        uint32_t mx = on ? min(L.cnt, LIST_CAP) : 0u;
+        const uint32_t mine = mx;
+#pragma unroll
+        for (int o_ = 16; o_ > 0; o_ >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o_));
+        if (on) kb_reset(kt, kj);
+        for (uint32_t e = 0; e < mx; ++e) {
+            if (e < mine) {
+                const uint2 q = L.base[e * 32 + lane];
+                const float t = __uint_as_float(q.x);
+                if (t > w && t < kt[KBUF - 1]) kb_insert(kt, kj, t, q.y);
+            }
+        }
+    };
+
     for (int it = 0;; ++it) {
-        if (!(w < sc.tmax) || kt[0] == FLT_MAX) done = true;  // forward_pass.cu:55,80-83
-        if (!__any_sync(0xffffffffu, !done)) break;
+        if (!(w < sc.tmax)) done = true;  // forward_pass.cu:55
+        select_batch(!done);
+        // a batch that is not full is only final if the list holds every hit beyond the window; otherwise the ray
+        // has more than LIST_CAP hits: collect the next LIST_CAP nearest with one more walk, then select again
+        const bool refill = !done && kt[KBUF - 1] == FLT_MAX && L.cnt > LIST_CAP;
+        if (__any_sync(0xffffffffu, refill)) {
+            if (refill) list_reset(L);
+            int dummy_acc = 0;
+            float dummy_T = 1.0f;
+            if (lane_walk) traverse_lane<false>(c.bvh, sc, o, d, idir, refill, w, L, dummy_T, dummy_acc, n_trav);
+            else traverse<false>(c.bvh, sc, o, d, idir, refill, w, L, dummy_T, dummy_acc, n_trav, s_rec);
+            select_batch(refill);
+        }
+        if (kt[0] == FLT_MAX) done = true;  // forward_pass.cu:80-83
         // one hit-log chunk per warp per batch (slot-major so that 32 lanes write 512 contiguous bytes)
         float4 *chunk = nullptr;
         if (grads) {
@@ -353,14 +407,14 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
         }
         // the batch goes through shared memory so that the composite loop can index it dynamically (small code)
 #pragma unroll
-        for (int i = 0; i < KBUF; ++i) s_kt[wib][i * 32 + lane] = kt[i], s_kj[wib][i * 32 + lane] = kj[i];
+        for (int i = 0; i < KBUF; ++i) s_kt[i * 32 + lane] = kt[i], s_kj[i * 32 + lane] = kj[i];
         for (int i = 0; i < KBUF; ++i) {
             if (!__any_sync(0xffffffffu, !done)) break;
             if (!done) {
-                const float t = s_kt[wib][i * 32 + lane];
+                const float t = s_kt[i * 32 + lane];
                 w = fmaxf(w, t);  // forward_pass.cu:89
                 if (t < sc.tmax) {
-                    const uint32_t j = s_kj[wib][i * 32 + lane];
+                    const uint32_t j = s_kj[i * 32 + lane];
                     const float4 r0 = __ldg(&c.bvh.records[4 * (size_t)j + 0]);
                     const float4 r1 = __ldg(&c.bvh.records[4 * (size_t)j + 1]);
                     const float4 r2 = __ldg(&c.bvh.records[4 * (size_t)j + 2]);
@@ -390,11 +444,6 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
         if (it + 1 >= MAX_ITERATIONS) done = true;
         if (!(w < sc.tmax)) done = true;
         if (!__any_sync(0xffffffffu, !done)) break;
-        kb_reset(kt, kj);
-        int dummy_acc = 0;
-        float dummy_T = 1.0f;
-        if (lane_walk) traverse_lane<false>(c.bvh, sc, o, d, idir, !done, w, kt, kj, dummy_T, dummy_acc, n_trav);
-        else traverse<false>(c.bvh, sc, o, d, idir, !done, w, kt, kj, dummy_T, dummy_acc, n_trav, s_rec[wib]);
     }
 
     if (lane == 0) {
@@ -510,6 +559,28 @@ __global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int 
     if (lane == 0) c.warp_mask[(size_t)step * c.num_warps + warp] = smask;
 }
 
+// Persistent launch: as many blocks as fit on the machine, every warp fetches the next 32-ray group (an 8x4 tile at
+// step 0, 32 compacted rays at a bounce step) from a counter until the step is done; a resident warp owns one hit-list
+// region for its whole life, so the lists of a step occupy a few tens of MB and stay in L2.
+__global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int step, const int grads) {
+    __shared__ float s_kt[4][KBUF * 32];
+    __shared__ uint32_t s_kj[4][KBUF * 32];
+    __shared__ float4 s_rec[4][FAT * 4];
+    const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int B = min(*c.p.config.num_bounces, (int)c.S - 1);  // shaders.cu:85
+    if (step > B) return;
+    const uint32_t groups = step == 0 ? c.num_warps : (c.ray_count[step] + 31) / 32;
+    uint2 *list = c.hitlist + (size_t)(blockIdx.x * 4 + wib) * LIST_CAP * 32;
+    while (true) {
+        uint32_t g = 0;
+        if (lane == 0) g = atomicAdd(&c.work_counter[step], 1u);
+        g = __shfl_sync(0xffffffffu, g, 0);
+        if (g >= groups) break;
+        trace_warp(c, step, grads, g, lane, s_kt[wib], s_kj[wib], s_rec[wib], list);
+        __syncwarp();
+    }
+}
+
 // ---- no-grad epilogue: accumulate + write every plane of every step (shaders.cu:163-169, framebuffer.h:104-143)
 __global__ void __launch_bounds__(256) k_resolve(const TraceCtx c) {
     const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
@@ -593,6 +664,8 @@ static int make_ctx(const EgrParams *p, TraceCtx &c) {
     c.warp_mask = (uint32_t *)(sb + L.warp_mask);
     c.warp_off = (uint32_t *)(sb + L.warp_off);
     c.ray_count = (uint32_t *)(sb + L.ray_count);
+    c.work_counter = (uint32_t *)(sb + L.work_counter);
+    c.hitlist = (uint2 *)(sb + L.hitlist);
     c.P = L.P, c.S = L.S, c.tiles_x = tiles_x(p->image_width), c.num_warps = L.num_warps;
     {
         const char *e = getenv("EGR_FORCE_WALK");  // debugging aid: 1 = warp-uniform walk everywhere, 2 = per-lane
@@ -603,6 +676,17 @@ static int make_ctx(const EgrParams *p, TraceCtx &c) {
 }
 
 int launch_backward_impl(const TraceCtx &c, cudaStream_t st);
+
+// Blocks of k_trace_step the current device keeps resident (occupancy x SM count), capped by the hit-list scratch.
+static uint32_t resident_blocks() {
+    int dev = 0, sms = 0, per_sm = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return 1;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_step, 128, 0);
+    const uint32_t nb = (uint32_t)max(1, sms * per_sm);
+    return min(nb, (uint32_t)(MAX_RESIDENT_WARPS / 4));
+}
+
 int launch_hitlog_export(const TraceCtx &c, int step, int cap, int32_t *ids, float *ts, int32_t *counts, cudaStream_t st);
 
 }  // namespace egr
@@ -633,7 +717,7 @@ extern "C" int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32
         if (rc) return rc;
         k_begin<<<(c.P + 255) / 256, 256, 0, st>>>(c, grads_enabled);
     }
-    const uint32_t blocks = (c.num_warps + 3) / 4;
+    const uint32_t blocks = min((c.num_warps + 3) / 4, resident_blocks());
     for (uint32_t s = 0; s < c.S; ++s)
         if (phase_mask & EGR_PHASE_STEP(s)) {
             if (s > 0) k_scan_spawned<<<1, 1024, 0, st>>>(c, (int)s);

@@ -366,3 +366,36 @@ def test_cuda_vs_committed_reference_vectors():
     gr = H.gpu_grads(rt)
     for k in ("dL_dnormal", "dL_df0", "dL_droughness"):
         assert H.rel_err(gr[k], g["ref_" + k]) <= TOL_GRAD, (k, H.rel_err(gr[k], g["ref_" + k]))
+
+
+def test_long_rays_beyond_the_hit_list():
+    """Rays with far more than 64 accepted hits (the per-ray hit list holds the 64 nearest; longer rays need further
+    collection walks) and several 16-wide batches: hit-ID lists still bit-exact, planes and gradients in tolerance."""
+    import torch
+
+    W, Hh = 32, 24
+    g = np.random.default_rng(3)
+    sc = scenes.random_scene(6000, seed=9)
+    sc["scale"] += 1.1
+    sc["opacity"] = g.uniform(-4.0, -2.5, (6000, 1)).astype(np.float32)  # translucent: T stays above the threshold
+    cam = scenes.random_camera(W, Hh)
+    cfg = dict(num_bounces=1, jitter_primary_rays=True)
+    rt = H.make_gpu_raytracer(sc, cam, cfg, hit_capacity=8_000_000)
+    tg = scenes.random_targets(W, Hh)
+    H.set_targets(rt, tg)
+    with torch.enable_grad():
+        rt.raytrace()
+    out = H.gpu_outputs(rt)
+    assert out["hitlog_status"][1] == 0
+    ocfg = orc.make_config(num_bounces=1, jitter_primary_rays=1)
+    cap = 400
+    ref = _pinned_oracle(rt, sc, cam, W, Hh, ocfg, out, 1, hit_cap=cap, grads=True, targets=tg)
+    assert ref["hit_counts"].max() > 100 and (ref["hit_counts"][0] > 64).mean() > 0.25
+    for step in range(2):
+        ids, ts, counts = rt.export_hit_lists(step, cap)
+        assert np.array_equal(counts.cpu().numpy().reshape(Hh, W), ref["hit_counts"][step]), step
+        assert np.array_equal(ids.cpu().numpy().reshape(Hh, W, cap), ref["hit_ids"][step]), step
+    assert np.array_equal(out["num_hits_per_pixel"], ref["num_hits_per_pixel"])
+    gr = H.gpu_grads(rt)
+    for k in list(H.GRAD_MAP) + ["total_weight"]:
+        assert H.rel_err(gr[k], ref[k]) <= TOL_GRAD, (k, H.rel_err(gr[k], ref[k]))
