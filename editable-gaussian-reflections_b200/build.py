@@ -18,7 +18,7 @@ HEADERS = ["egr_common.cuh", "egr_trace.cuh", os.path.join("..", "..", "include"
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
     "--expt-relaxed-constexpr", "-Xcudafe", "--diag_suppress=177",
-]
+] + os.environ.get("EGR_NVCC_EXTRA", "").split()
 
 
 def _nvcc() -> str:

@@ -21,7 +21,26 @@ __device__ __forceinline__ void red_add_v4(float *addr, float a, float b, float 
 template <int NV>
 __device__ __forceinline__ void flush_grads(float *grad_records, uint32_t id, bool has, float (&g)[24]) {
     const uint32_t lane = threadIdx.x & 31;
+#ifdef EGR_NO_AGGREGATION
+    if (has) {
+        float *dst = grad_records + (size_t)id * EGR_GRAD_STRIDE;
+#pragma unroll
+        for (int k = 0; k < NV; k += 4) red_add_v4(dst + k, g[k], g[k + 1], g[k + 2], g[k + 3]);
+    }
+    return;
+#endif
     unsigned peers = __match_any_sync(0xffffffffu, has ? id : (0x80000000u | lane));
+    // The tree below costs ~3 shuffle rounds over all 24 values; it only pays when many lanes of the warp hit the
+    // same Gaussian (large foreground Gaussians, where same-address reductions would serialise in L2).  With
+    // mostly distinct Gaussians the 128-bit reductions go out directly.
+    if (!__any_sync(0xffffffffu, __popc(peers) >= 8)) {
+        if (has) {
+            float *dst = grad_records + (size_t)id * EGR_GRAD_STRIDE;
+#pragma unroll
+            for (int k = 0; k < NV; k += 4) red_add_v4(dst + k, g[k], g[k + 1], g[k + 2], g[k + 3]);
+        }
+        return;
+    }
     const unsigned lt = (1u << lane) - 1u;
     const unsigned gt = ~lt & ~(1u << lane);
     const bool leader = has && (peers & lt) == 0;
