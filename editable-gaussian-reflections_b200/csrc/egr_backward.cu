@@ -154,8 +154,8 @@ __global__ void __launch_bounds__(128) k_backward(const TraceCtx c, const int st
                     const float4 r3 = __ldg(&c.bvh.records[4 * (size_t)j + 3]);
                     HitEval h;
                     eval_hit(r0, r1, r2, r3, o, d, tmin, tmax, exp_power, h);
-                    const float sf = r3.x, sigma = r3.y;
-                    id = __float_as_uint(r3.z);
+                    const float sf = r1.w, sigma = r2.w;
+                    id = __float_as_uint(r3.w);
                     const float gv = h.gaussval;
                     const float4 a0 = __ldg(&c.bvh.appearance[3 * (size_t)j + 0]);
                     const f3 c_rgb = mk3(a0.x, a0.y, a0.z);
@@ -199,8 +199,8 @@ __global__ void __launch_bounds__(128) k_backward(const TraceCtx c, const int st
                     const float sqn = dotp(h.x, h.x);
                     const float dsq = gv * det_pow(sqn, exp_power - 1.0f);
                     const f3 dxl = -h.x * dsq * dL_dg;
-                    const f3 dxw = mk3(dotp(mk3(r0.x, r1.x, r2.x), dxl), dotp(mk3(r0.y, r1.y, r2.y), dxl),
-                                       dotp(mk3(r0.z, r1.z, r2.z), dxl)) *
+                    const f3 dxw = mk3(dotp(mk3(r1.x, r2.x, r3.x), dxl), dotp(mk3(r1.y, r2.y, r3.y), dxl),
+                                       dotp(mk3(r1.z, r2.z, r3.z), dxl)) *
                                    sf;
                     const f3 l0 = -dxw.x * h.x, l1 = -dxw.y * h.x, l2 = -dxw.z * h.x;
                     // scale / rotation (backward_pass.cu:169-207) from the raw parameters
@@ -272,7 +272,7 @@ k_hitlog_export(const TraceCtx c, const int step, const int cap, int32_t *ids, f
             if (idx < nh && idx < cap) {
                 const float4 e = entries[slot * 32 + lane];
                 const uint32_t j = __float_as_uint(e.x);
-                ids[(size_t)pix * cap + idx] = (int32_t)__float_as_uint(c.bvh.records[4 * (size_t)j + 3].z);
+                ids[(size_t)pix * cap + idx] = (int32_t)__float_as_uint(c.bvh.records[4 * (size_t)j + 3].w);
                 if (ts) ts[(size_t)pix * cap + idx] = e.y;
             }
         }

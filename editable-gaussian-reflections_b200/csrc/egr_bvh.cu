@@ -213,21 +213,18 @@ __global__ void __launch_bounds__(256) k_refit(BvhView bvh, EgrGaussians g, EgrC
     bool visible = sf > 0.0f && S.x > 0.0f && S.y > 0.0f && S.z > 0.0f && isfinite(norm) && norm > 0.0f &&
                    isfinite(mu.x) && isfinite(mu.y) && isfinite(mu.z) && isfinite(S.x) && isfinite(S.y) && isfinite(S.z);
     float Sv[3] = {S.x, S.y, S.z};
-    float4 rec[3];
-    float *rf = reinterpret_cast<float *>(rec);
+    // geometry record (layout: eval_hit in egr_common.cuh)
+    const float rad = fmaxf(S.x, fmaxf(S.y, S.z)) * 1.001f;  // bounding sphere of the proxy ellipsoid, inflated
     float muv[3] = {mu.x, mu.y, mu.z};
+    float Wr[3][3];
 #pragma unroll
-    for (int rr = 0; rr < 3; ++rr) {
+    for (int rr = 0; rr < 3; ++rr)
 #pragma unroll
-        for (int c = 0; c < 3; ++c) rf[4 * rr + c] = visible ? R[c][rr] / Sv[rr] : 0.0f;
-        rf[4 * rr + 3] = muv[rr];
-    }
-    bvh.records[4 * (size_t)j + 0] = rec[0];
-    bvh.records[4 * (size_t)j + 1] = rec[1];
-    bvh.records[4 * (size_t)j + 2] = rec[2];
-    // .w: squared radius of the bounding sphere of the proxy ellipsoid (semi-axes S), slightly inflated; 0 = invisible
-    const float rad = fmaxf(S.x, fmaxf(S.y, S.z)) * 1.001f;
-    bvh.records[4 * (size_t)j + 3] = make_float4(sf, sigma, __uint_as_float(id), visible ? rad * rad : 0.0f);
+        for (int c = 0; c < 3; ++c) Wr[rr][c] = visible ? R[c][rr] / Sv[rr] : 0.0f;
+    bvh.records[4 * (size_t)j + 0] = make_float4(mu.x, mu.y, mu.z, visible ? rad * rad : 0.0f);
+    bvh.records[4 * (size_t)j + 1] = make_float4(Wr[0][0], Wr[0][1], Wr[0][2], sf);
+    bvh.records[4 * (size_t)j + 2] = make_float4(Wr[1][0], Wr[1][1], Wr[1][2], sigma);
+    bvh.records[4 * (size_t)j + 3] = make_float4(Wr[2][0], Wr[2][1], Wr[2][2], __uint_as_float(id));
 
     // world box of the image of [-1,1]^3 under M = R diag(S), inflated so that it is strictly conservative w.r.t.
     // the exact local-space test (which alone defines the candidate set)

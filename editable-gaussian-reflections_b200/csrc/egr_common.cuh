@@ -58,7 +58,7 @@ struct BvhView {
     uint32_t n, num_nodes;
     float *bounds;          // [6] scene bounds of the means (min xyz, max xyz) used for the Morton grid
     uint32_t *sorted_ids;   // [n] leaf j -> Gaussian id
-    float4 *records;        // [n][4] geometry record in leaf order (layout: include/egr_b200.h)
+    float4 *records;        // [n][4] geometry record in leaf order (layout: eval_hit below)
     float4 *appearance;     // [n][3] activated rgb,rough | normal,_ | f0,_
     float4 *nodes;          // [num_nodes][2]: (bmin.xyz, skip) (bmax.xyz, leaf | FIRST_LEAF_FLAG+first leaf)
     uint32_t *parents;      // [num_nodes] preorder index of the parent
@@ -192,6 +192,7 @@ __device__ __forceinline__ float det_exp(float u) {
     return p * __int_as_float((e + 127) << 23);
 }
 __device__ __forceinline__ float det_pow(float d, float p) {
+    if (p == 3.0f) return (d * d) * d;  // the reference's default exp_power; same left-to-right product as below
     int ip = (int)p;
     if ((float)ip == p && ip >= 1 && ip <= 8) {
         float r = d;
@@ -223,14 +224,16 @@ struct HitEval {
     f3 x;   // local hit scaled by sf (reference: local_hit)
     f3 dh;  // normalised object-space direction
 };
-// Reference: csrc/shaders.cu:9-75 (__intersection__gaussian).  `r0..r3` is the packed geometry record.
+// Reference: csrc/shaders.cu:9-75 (__intersection__gaussian).  `r0..r3` is the packed geometry record:
+//   r0 = (mean.xyz, squared bounding radius; 0 = invisible)   r1 = (W row 0, sf)   r2 = (W row 1, sigma)
+//   r3 = (W row 2, Gaussian id bits)          W = world -> object = diag(1/S) R^T
 // Returns false when rejected.  Every mul-add on this path is an explicit fmaf so that the oracle reproduces it
 // bit for bit.  The backface test (needs the normal) is done by the caller with `dh`.
 __device__ __forceinline__ bool eval_hit(
     const float4 r0, const float4 r1, const float4 r2, const float4 r3, f3 o, f3 d, float tmin, float tmax,
     float exp_power, HitEval &h) {
-    f3 w0 = mk3(r0.x, r0.y, r0.z), w1 = mk3(r1.x, r1.y, r1.z), w2 = mk3(r2.x, r2.y, r2.z);
-    f3 p = o - mk3(r0.w, r1.w, r2.w);
+    f3 w0 = mk3(r1.x, r1.y, r1.z), w1 = mk3(r2.x, r2.y, r2.z), w2 = mk3(r3.x, r3.y, r3.z);
+    f3 p = o - mk3(r0.x, r0.y, r0.z);
     f3 ol = mk3(dot3(w0, p), dot3(w1, p), dot3(w2, p));
     f3 dl = mk3(dot3(w0, d), dot3(w1, d), dot3(w2, d));
     if (dot3(ol, dl) > 0.0f) return false;
@@ -250,7 +253,7 @@ __device__ __forceinline__ bool eval_hit(
         float tfar = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
         if (!(tfar >= tmin && tnear <= tmax)) return false;
     }
-    float sf = r3.x, sigma = r3.y;
+    float sf = r1.w, sigma = r2.w;
     f3 x = xu * sf;
     float d2 = dot3(x, x);
     float g = det_exp(-det_pow(d2, exp_power) / (2.0f * exp_power));

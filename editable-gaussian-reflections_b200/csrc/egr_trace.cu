@@ -72,17 +72,22 @@ __device__ __forceinline__ void list_add(LaneList &L, const uint32_t lane, const
 
 // One candidate Gaussian against one ray: cheap conservative bounding-sphere reject, then the exact test, the
 // exact total transmittance (pass 0) and the hit list.
-template <bool PASS0>
+template <bool PASS0, bool SHARED>
 __device__ __forceinline__ void test_candidate(
-    const BvhView &bvh, const StepCfg &sc, const float4 r0, const float4 r1, const float4 r2, const float4 r3,
-    const uint32_t leaf, const f3 o, const f3 d, const float w, LaneList &L, float &T_full, int &n_acc, int &n_trav) {
+    const BvhView &bvh, const StepCfg &sc, const float4 *rp, const uint32_t leaf, const f3 o, const f3 d, const float w,
+    LaneList &L, float &T_full, int &n_acc, int &n_trav) {
+    // only the first quad (centre + squared bounding radius) is needed to reject most candidates
+    const float4 r0 = SHARED ? rp[0] : __ldg(rp);
     // the accepted hit point lies on the forward ray and inside the proxy ellipsoid, hence inside its bounding
     // sphere: reject when the line misses the sphere, or when the sphere lies wholly behind the origin
-    const f3 p = mk3(r0.w, r1.w, r2.w) - o;
+    const f3 p = mk3(r0.x, r0.y, r0.z) - o;
     const f3 cr = cross3(p, d);
-    if (!(dotp(cr, cr) <= r3.w)) return;
-    if (r3.w == 0.0f) return;  // invisible Gaussian (radius^2 = 0) that happens to sit exactly on the ray
-    if (dotp(p, d) < 0.0f && dotp(p, p) > r3.w) return;
+    if (!(dotp(cr, cr) <= r0.w)) return;
+    if (r0.w == 0.0f) return;  // invisible Gaussian (radius^2 = 0) that happens to sit exactly on the ray
+    if (dotp(p, d) < 0.0f && dotp(p, p) > r0.w) return;
+    const float4 r1 = SHARED ? rp[1] : __ldg(rp + 1);
+    const float4 r2 = SHARED ? rp[2] : __ldg(rp + 2);
+    const float4 r3 = SHARED ? rp[3] : __ldg(rp + 3);
     n_trav++;
     HitEval h;
     bool ok = eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);
@@ -145,9 +150,7 @@ __device__ __forceinline__ void traverse(
         for (uint32_t q = lane; q < nl * 4; q += 32) s_rec[q] = __ldg(&bvh.records[4 * (size_t)first + q]);
         __syncwarp();
         for (uint32_t k = 0; k < nl; ++k) {
-            if (hit)
-                test_candidate<PASS0>(bvh, sc, s_rec[4 * k], s_rec[4 * k + 1], s_rec[4 * k + 2], s_rec[4 * k + 3],
-                                      first + k, o, d, w, L, T_full, n_acc, n_trav);
+            if (hit) test_candidate<PASS0, true>(bvh, sc, s_rec + 4 * k, first + k, o, d, w, L, T_full, n_acc, n_trav);
         }
         node = skip;
     }
@@ -201,11 +204,8 @@ __device__ __forceinline__ void traverse_lane(
         if (!__any_sync(0xffffffffu, leaf != NO_LEAF)) break;
         if (leaf != NO_LEAF) {
             for (uint32_t k = 0; k < leaf_n; ++k) {
-                const float4 r0 = __ldg(&bvh.records[4 * (size_t)(leaf + k) + 0]);
-                const float4 r1 = __ldg(&bvh.records[4 * (size_t)(leaf + k) + 1]);
-                const float4 r2 = __ldg(&bvh.records[4 * (size_t)(leaf + k) + 2]);
-                const float4 r3 = __ldg(&bvh.records[4 * (size_t)(leaf + k) + 3]);
-                test_candidate<PASS0>(bvh, sc, r0, r1, r2, r3, leaf + k, o, d, w, L, T_full, n_acc, n_trav);
+                test_candidate<PASS0, false>(bvh, sc, bvh.records + 4 * (size_t)(leaf + k), leaf + k, o, d, w, L, T_full,
+                                             n_acc, n_trav);
             }
         }
     }
@@ -562,7 +562,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
 // Persistent launch: as many blocks as fit on the machine, every warp fetches the next 32-ray group (an 8x4 tile at
 // step 0, 32 compacted rays at a bounce step) from a counter until the step is done; a resident warp owns one hit-list
 // region for its whole life, so the lists of a step occupy a few tens of MB and stay in L2.
-__global__ void __launch_bounds__(128) k_trace_step(const TraceCtx c, const int step, const int grads) {
+__global__ void __launch_bounds__(128, 5) k_trace_step(const TraceCtx c, const int step, const int grads) {
     __shared__ float s_kt[4][KBUF * 32];
     __shared__ uint32_t s_kj[4][KBUF * 32];
     __shared__ float4 s_rec[4][FAT * 4];

@@ -192,7 +192,8 @@ int orc_num_threads() {
 #endif
 }
 
-// Record layout (16 floats): W row0 xyz, mean.x | W row1 xyz, mean.y | W row2 xyz, mean.z | sf, sigma, id-bits, visible
+// Record layout (16 floats, same as the CUDA geometry record): mean.xyz, squared bounding radius (0 = invisible) |
+// W row0 xyz, sf | W row1 xyz, sigma | W row2 xyz, id bits        (W = world -> object = diag(1/S) R^T)
 // bvh_wrapper.cu:9-59 (transform, visibility), kernel.cu:3-6 (scaling factor), activations.cu:5,59,67-69
 void orc_prepare(const OrcScene *sc, const OrcConfig *cfg, float *rec) {
     const float k = 2.0f * cfg->exp_power;
@@ -215,15 +216,15 @@ void orc_prepare(const OrcScene *sc, const OrcConfig *cfg, float *rec) {
         bool visible = sf > 0.0f && S.x > 0.0f && S.y > 0.0f && S.z > 0.0f && std::isfinite(norm) && norm > 0.0f;
         float Sv[3] = {S.x, S.y, S.z};
         float *o = rec + 16 * (size_t)i;
-        for (int rr = 0; rr < 3; ++rr) {
-            for (int c = 0; c < 3; ++c) o[4 * rr + c] = visible ? R[c][rr] / Sv[rr] : 0.0f;
-            o[4 * rr + 3] = sc->mean[3 * i + rr];
-        }
-        o[12] = sf;
-        o[13] = sigma;
+        float rad = fmaxf(S.x, fmaxf(S.y, S.z)) * 1.001f;
+        o[0] = sc->mean[3 * i], o[1] = sc->mean[3 * i + 1], o[2] = sc->mean[3 * i + 2];
+        o[3] = visible ? rad * rad : 0.0f;
+        for (int rr = 0; rr < 3; ++rr)
+            for (int c = 0; c < 3; ++c) o[4 + 4 * rr + c] = visible ? R[c][rr] / Sv[rr] : 0.0f;
+        o[7] = sf;
+        o[11] = sigma;
         uint32_t id = (uint32_t)i;
-        std::memcpy(&o[14], &id, 4);
-        o[15] = visible ? 1.0f : 0.0f;
+        std::memcpy(&o[15], &id, 4);
     }
 }
 
@@ -247,9 +248,9 @@ struct RayResult {
 // shaders.cu:9-75 for one (ray, Gaussian) pair given the packed record.  Returns true when accepted.
 inline bool candidate(
     const float *rec, const float *normals, const OrcConfig &cfg, int step, f3 o, f3 d, float tmin, float tmax, Hit &h) {
-    if (rec[15] == 0.0f) return false;
-    f3 w0 = mk(rec[0], rec[1], rec[2]), w1 = mk(rec[4], rec[5], rec[6]), w2 = mk(rec[8], rec[9], rec[10]);
-    f3 mu = mk(rec[3], rec[7], rec[11]);
+    if (rec[3] == 0.0f) return false;
+    f3 w0 = mk(rec[4], rec[5], rec[6]), w1 = mk(rec[8], rec[9], rec[10]), w2 = mk(rec[12], rec[13], rec[14]);
+    f3 mu = mk(rec[0], rec[1], rec[2]);
     f3 p = o - mu;
     f3 ol = mk(dot3(w0, p), dot3(w1, p), dot3(w2, p));
     f3 dl = mk(dot3(w0, d), dot3(w1, d), dot3(w2, d));
@@ -274,12 +275,12 @@ inline bool candidate(
         if (!(tfar >= tmin && tnear <= tmax)) return false;
     }
     uint32_t id;
-    std::memcpy(&id, &rec[14], 4);
+    std::memcpy(&id, &rec[15], 4);
     if (step != 0 && t < cfg.backfacing_max_dist) {  // shaders.cu:53-61 (object-space dh vs world normal, as written)
         f3 nrm = ld3(normals, id);
         if (sqrtf(dot3(nrm, nrm)) > cfg.backfacing_invalid_normal_threshold && dot3(nrm, dh) > 0.0f) return false;
     }
-    float sf = rec[12], sigma = rec[13];
+    float sf = rec[7], sigma = rec[11];
     f3 x = xu * sf;                                             // shaders.cu:64
     float d2 = dot3(x, x);
     float g = det_exp(-det_pow(d2, cfg.exp_power) / (2.0f * cfg.exp_power));  // kernel.cu:8-12
@@ -356,15 +357,16 @@ void orc_render(
     std::vector<BoundSphere> bs(n);
     for (int i = 0; i < n; ++i) {
         const float *r = recs + 16 * (size_t)i;
-        bs[i].c = mk(r[3], r[7], r[11]);
-        if (r[15] == 0.0f) {
+        bs[i].c = mk(r[0], r[1], r[2]);
+        if (r[3] == 0.0f) {
             bs[i].r2 = -1.0f;
             continue;
         }
         // rows of W have norm 1/S_r; the unit box maps into a sphere of radius sqrt(3)*max S
         float smax = 0.0f;
         for (int rr = 0; rr < 3; ++rr) {
-            float nr = sqrtf(r[4 * rr] * r[4 * rr] + r[4 * rr + 1] * r[4 * rr + 1] + r[4 * rr + 2] * r[4 * rr + 2]);
+            const float *wr = r + 4 + 4 * rr;
+            float nr = sqrtf(wr[0] * wr[0] + wr[1] * wr[1] + wr[2] * wr[2]);
             smax = fmaxf(smax, 1.0f / nr);
         }
         float rad = 1.7320508f * smax * 1.001f + 1e-6f;
@@ -618,7 +620,7 @@ void orc_render(
                             c_r = fminf(fmaxf(0.0f, sc->roughness[id]), 1.0f);
                         }
                         const float *rec = recs + 16 * (size_t)id;
-                        float sigma = rec[13], sf = rec[12];
+                        float sigma = rec[11], sf = rec[7];
                         f3 sc_e = mk(expf(sc->scale[3 * id]), expf(sc->scale[3 * id + 1]), expf(sc->scale[3 * id + 2]));
                         float qr = sc->rotation[4 * id], qx = sc->rotation[4 * id + 1], qy = sc->rotation[4 * id + 2],
                               qz = sc->rotation[4 * id + 3];
@@ -658,7 +660,7 @@ void orc_render(
                         float dsq = gv * det_pow(sqn, kexp - 1.0f);  // backward_pass.cu:157
                         f3 dxl = -h.x * dsq * dL_dg;
                         // world_to_local columns dotted with dxl (backward_pass.cu:160-167)
-                        f3 w0 = mk(rec[0], rec[1], rec[2]), w1 = mk(rec[4], rec[5], rec[6]), w2 = mk(rec[8], rec[9], rec[10]);
+                        f3 w0 = mk(rec[4], rec[5], rec[6]), w1 = mk(rec[8], rec[9], rec[10]), w2 = mk(rec[12], rec[13], rec[14]);
                         f3 dxw = mk(dotp(mk(w0.x, w1.x, w2.x), dxl), dotp(mk(w0.y, w1.y, w2.y), dxl),
                                     dotp(mk(w0.z, w1.z, w2.z), dxl)) *
                                  sf;
