@@ -67,7 +67,7 @@ __device__ __forceinline__ void flush_grads(float *grad_records, uint32_t id, bo
     }
 }
 
-__global__ void __launch_bounds__(128) k_backward(const TraceCtx c, const int step) {
+__global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int step) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31;
     if (warp >= c.num_warps) return;
@@ -208,7 +208,8 @@ __global__ void __launch_bounds__(128) k_backward(const TraceCtx c, const int st
                     const f3 sc_e = mk3(expf(sraw.x), expf(sraw.y), expf(sraw.z));
                     const float4 q4 = __ldg(&reinterpret_cast<const float4 *>(gs.rotation)[id]);
                     const float qn = sqrtf(q4.x * q4.x + q4.y * q4.y + q4.z * q4.z + q4.w * q4.w);
-                    const float r = q4.x / qn, xq = q4.y / qn, yq = q4.z / qn, zq = q4.w / qn;
+                    const float iqn = 1.0f / qn;
+                    const float r = q4.x * iqn, xq = q4.y * iqn, yq = q4.z * iqn, zq = q4.w * iqn;
                     const float R00 = 1.f - 2.f * (yq * yq + zq * zq), R01 = 2.f * (xq * yq - r * zq),
                                 R02 = 2.f * (xq * zq + r * yq);
                     const float R10 = 2.f * (xq * yq + r * zq), R11 = 1.f - 2.f * (xq * xq + zq * zq),
@@ -217,9 +218,10 @@ __global__ void __launch_bounds__(128) k_backward(const TraceCtx c, const int st
                                 R22 = 1.f - 2.f * (xq * xq + yq * yq);
                     const f3 Sg = sc_e * sf * gsf;
                     const f3 den = sc_e * sf + mk3(eps_scale_grad, eps_scale_grad, eps_scale_grad);
-                    const f3 rot0 = mk3(R00 * Sg.x, R01 * Sg.y, R02 * Sg.z) / den;
-                    const f3 rot1 = mk3(R10 * Sg.x, R11 * Sg.y, R12 * Sg.z) / den;
-                    const f3 rot2 = mk3(R20 * Sg.x, R21 * Sg.y, R22 * Sg.z) / den;
+                    const f3 sod = Sg / den;  // one division per axis instead of one per matrix entry
+                    const f3 rot0 = mk3(R00, R01, R02) * sod;
+                    const f3 rot1 = mk3(R10, R11, R12) * sod;
+                    const f3 rot2 = mk3(R20, R21, R22) * sod;
                     const f3 g_scale = (l0 * rot0 + l1 * rot1 + l2 * rot2) * sc_e;
                     const f3 dr0 = l0 * sc_e, dr1 = l1 * sc_e, dr2 = l2 * sc_e;
                     const float dLr =
@@ -231,7 +233,7 @@ __global__ void __launch_bounds__(128) k_backward(const TraceCtx c, const int st
                     const float dLz = 2.f * xq * (dr0.z + dr2.x) + 2.f * yq * (dr1.z + dr2.y) -
                                       4.f * zq * (dr0.x + dr1.y) + 2.f * r * (dr1.x - dr0.y);
                     const float dq = dLr * q4.x + dLx * q4.y + dLy * q4.z + dLz * q4.w;  // activations.cu:71-73
-                    const float i3 = 1.0f / (qn * qn * qn), i1 = 1.0f / qn;
+                    const float i1 = iqn, i3 = (iqn * iqn) * iqn;
                     g[0] = -dxw.x, g[1] = -dxw.y, g[2] = -dxw.z;  // mean (backward_pass.cu:175)
                     g[3] = g_op;
                     g[4] = g_scale.x, g[5] = g_scale.y, g[6] = g_scale.z;
