@@ -74,10 +74,9 @@ __device__ __forceinline__ void list_add(LaneList &L, const uint32_t lane, const
 // exact total transmittance (pass 0) and the hit list.
 template <bool PASS0, bool SHARED>
 __device__ __forceinline__ void test_candidate(
-    const BvhView &bvh, const StepCfg &sc, const float4 *rp, const uint32_t leaf, const f3 o, const f3 d, const float w,
-    LaneList &L, float &T_full, int &n_acc, int &n_trav) {
-    // only the first quad (centre + squared bounding radius) is needed to reject most candidates
-    const float4 r0 = SHARED ? rp[0] : __ldg(rp);
+    const BvhView &bvh, const StepCfg &sc, const float4 *rp, const float4 r0, const uint32_t leaf, const f3 o, const f3 d,
+    const float w, LaneList &L, float &T_full, int &n_acc, int &n_trav) {
+    // only the first quad r0 (centre + squared bounding radius) is needed to reject most candidates
     // the accepted hit point lies on the forward ray and inside the proxy ellipsoid, hence inside its bounding
     // sphere: reject when the line misses the sphere, or when the sphere lies wholly behind the origin
     const f3 p = mk3(r0.x, r0.y, r0.z) - o;
@@ -150,7 +149,8 @@ __device__ __forceinline__ void traverse(
         for (uint32_t q = lane; q < nl * 4; q += 32) s_rec[q] = __ldg(&bvh.records[4 * (size_t)first + q]);
         __syncwarp();
         for (uint32_t k = 0; k < nl; ++k) {
-            if (hit) test_candidate<PASS0, true>(bvh, sc, s_rec + 4 * k, first + k, o, d, w, L, T_full, n_acc, n_trav);
+            if (hit)
+                test_candidate<PASS0, true>(bvh, sc, s_rec + 4 * k, s_rec[4 * k], first + k, o, d, w, L, T_full, n_acc, n_trav);
         }
         node = skip;
     }
@@ -203,9 +203,17 @@ __device__ __forceinline__ void traverse_lane(
         }
         if (!__any_sync(0xffffffffu, leaf != NO_LEAF)) break;
         if (leaf != NO_LEAF) {
-            for (uint32_t k = 0; k < leaf_n; ++k) {
-                test_candidate<PASS0, false>(bvh, sc, bvh.records + 4 * (size_t)(leaf + k), leaf + k, o, d, w, L, T_full,
-                                             n_acc, n_trav);
+            // the centre quads of four candidates are fetched together (independent loads), then tested
+            for (uint32_t k0 = 0; k0 < leaf_n; k0 += 4) {
+                float4 q[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    q[i] = k0 + i < leaf_n ? __ldg(bvh.records + 4 * (size_t)(leaf + k0 + i)) : make_float4(0, 0, 0, 0);
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (k0 + i < leaf_n)
+                        test_candidate<PASS0, false>(bvh, sc, bvh.records + 4 * (size_t)(leaf + k0 + i), q[i], leaf + k0 + i,
+                                                     o, d, w, L, T_full, n_acc, n_trav);
             }
         }
     }
@@ -243,6 +251,7 @@ __global__ void __launch_bounds__(256) k_begin(TraceCtx c, int grads) {
 // what keeps bounce rays of one warp coherent, and makes the ray order deterministic.
 __global__ void __launch_bounds__(1024) k_scan_spawned(const TraceCtx c, const int step) {
     __shared__ uint32_t s_part[1024];
+    if (step > min(*c.p.config.num_bounces, (int)c.S - 1)) return;
     const uint32_t *mask = c.warp_mask + (size_t)(step - 1) * c.num_warps;
     uint32_t *off = c.warp_off + (size_t)step * c.num_warps;
     const uint32_t n = c.num_warps, t = threadIdx.x;
@@ -350,8 +359,13 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
     LaneList L;
     L.base = list;
     list_reset(L);
-    if (lane_walk) traverse_lane<true>(c.bvh, sc, o, d, idir, alive, w, L, T_full, n_acc, n_trav);
-    else traverse<true>(c.bvh, sc, o, d, idir, alive, w, L, T_full, n_acc, n_trav, s_rec);
+    // A ray with a non-finite origin / direction (the reference's tangent frame, ggx_brdf.h:163, is 0/0 for a normal
+    // of exactly -z) is invalid for OptiX and finds nothing there; here it would pass every box test, so it is not
+    // walked at all: no hits, T = T_full = 1, the path ends at the normal-length test.
+    const bool ray_ok = isfinite(o.x + o.y + o.z + d.x + d.y + d.z) && dotp(d, d) > 0.0f;
+    const bool walk = alive && ray_ok;
+    if (lane_walk) traverse_lane<true>(c.bvh, sc, o, d, idir, walk, w, L, T_full, n_acc, n_trav);
+    else traverse<true>(c.bvh, sc, o, d, idir, walk, w, L, T_full, n_acc, n_trav, s_rec);
 
     uint32_t tail_chunk = 0xFFFFFFFFu, nbatches = 0;
     bool log_ok = grads != 0;

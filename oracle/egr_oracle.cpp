@@ -304,6 +304,9 @@ void trace_ray(
     out.hits.clear();
     out.T_full = 1.0f;
     out.n_accepted = 0;
+    // a ray with a non-finite origin / direction is invalid for optixTraverse and finds nothing (the reference's
+    // tangent frame, ggx_brdf.h:163, produces such rays when the shading normal is exactly -z)
+    if (!std::isfinite(o.x + o.y + o.z + d.x + d.y + d.z) || !(dotp(d, d) > 0.0f)) return;
     for (int i = 0; i < n; ++i) {
         // conservative prefilter (pure accelerator): the hit point lies inside the proxy's bounding sphere
         f3 pc = bs[i].c - o;

@@ -117,6 +117,8 @@ void optixTraverse(OptixTraversableHandle, float3 o, float3 d, float tmin, float
                    uint32_t &p4, uint32_t &p5, uint32_t &p6, uint32_t &p7) {
     uint32_t *pl[8] = {&p0, &p1, &p2, &p3, &p4, &p5, &p6, &p7};
     for (int i = 0; i < 8; ++i) ref_ts.payload[i] = pl[i];
+    // OptiX treats a ray with a non-finite origin / direction as invalid: nothing is traversed
+    if (!std::isfinite(o.x + o.y + o.z + d.x + d.y + d.z) || !(dot(d, d) > 0.0f)) return;
     for (uint32_t i = 0; i < ref_num_instances; ++i) {
         const RefInstance &in = ref_instances[i];
         if (!in.visible) continue;
