@@ -198,17 +198,21 @@ __global__ void __launch_bounds__(256) k_refit(BvhView bvh, EgrGaussians g, EgrC
     const float alpha_threshold = *cfg.alpha_threshold, exp_power = *cfg.exp_power, gsf = *cfg.global_scale_factor;
     const uint32_t id = bvh.sorted_ids[j];
     const float k = 2.0f * exp_power;
-    float sigma = 1.0f / (1.0f + expf(-g.opacity[id]));
-    float sf = sigma <= alpha_threshold ? 0.0f : powf(k * logf(sigma / alpha_threshold), 1.0f / k);
-    f3 s = mk3(expf(g.scale[3 * (size_t)id]), expf(g.scale[3 * (size_t)id + 1]), expf(g.scale[3 * (size_t)id + 2]));
+    // every transcendental goes through include/egr_detmath.h and every mul-add is an explicit fmaf, so that the
+    // CPU oracle reproduces these records bit for bit
+    float sigma = 1.0f / (1.0f + egr_det_exp(-g.opacity[id]));
+    float sf = sigma <= alpha_threshold ? 0.0f : egr_det_pow(k * egr_det_log(sigma / alpha_threshold), 1.0f / k);
+    f3 s = mk3(egr_det_exp(g.scale[3 * (size_t)id]), egr_det_exp(g.scale[3 * (size_t)id + 1]),
+               egr_det_exp(g.scale[3 * (size_t)id + 2]));
     f3 S = s * sf * gsf;
     const float4 q4 = reinterpret_cast<const float4 *>(g.rotation)[id];
     float r = q4.x, x = q4.y, y = q4.z, z = q4.w;
-    float norm = sqrtf(r * r + x * x + y * y + z * z);
+    float norm = sqrtf(fmaf(z, z, fmaf(y, y, fmaf(x, x, r * r))));
     r /= norm, x /= norm, y /= norm, z /= norm;
-    float R[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
-                     {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
-                     {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+    float R[3][3] = {
+        {fmaf(-2.f, fmaf(z, z, y * y), 1.f), 2.f * fmaf(x, y, -(r * z)), 2.f * fmaf(x, z, r * y)},
+        {2.f * fmaf(x, y, r * z), fmaf(-2.f, fmaf(z, z, x * x), 1.f), 2.f * fmaf(y, z, -(r * x))},
+        {2.f * fmaf(x, z, -(r * y)), 2.f * fmaf(y, z, r * x), fmaf(-2.f, fmaf(y, y, x * x), 1.f)}};
     f3 mu = ld3(g.mean, id);
     bool visible = sf > 0.0f && S.x > 0.0f && S.y > 0.0f && S.z > 0.0f && isfinite(norm) && norm > 0.0f &&
                    isfinite(mu.x) && isfinite(mu.y) && isfinite(mu.z) && isfinite(S.x) && isfinite(S.y) && isfinite(S.z);

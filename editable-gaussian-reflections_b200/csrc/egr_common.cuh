@@ -5,6 +5,7 @@
 #include <stdio.h>
 
 #include "../../include/egr_b200.h"
+#include "../../include/egr_detmath.h"
 
 namespace egr {
 
@@ -156,6 +157,15 @@ __host__ __device__ inline f3 div_s(f3 a, float s) {
 }
 // canonical dot product of the hit-ID-critical path (mirrored by the oracle)
 __host__ __device__ inline float dot3(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+// canonical (explicit-fma) forms used wherever the oracle has to reproduce the bits
+__host__ __device__ inline f3 fma3(f3 a, float s, f3 c) { return mk3(fmaf(a.x, s, c.x), fmaf(a.y, s, c.y), fmaf(a.z, s, c.z)); }
+__host__ __device__ inline f3 cross3c(f3 a, f3 b) {
+    return mk3(fmaf(a.y, b.z, -(a.z * b.y)), fmaf(a.z, b.x, -(a.x * b.z)), fmaf(a.x, b.y, -(a.y * b.x)));
+}
+__host__ __device__ inline f3 norm3c(f3 v) {
+    float inv = 1.0f / sqrtf(dot3(v, v));
+    return v * inv;
+}
 __host__ __device__ inline float dotp(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 __host__ __device__ inline f3 cross3(f3 a, f3 b) {
     return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
@@ -174,23 +184,8 @@ __device__ __forceinline__ void st3(float *p, size_t i, f3 v) {
     p[3 * i] = v.x, p[3 * i + 1] = v.y, p[3 * i + 2] = v.z;
 }
 
-// exp(u), u <= 0: Cody-Waite reduction + degree-7 Horner, IEEE-only sequence (bit-identical to the oracle's).
-__device__ __forceinline__ float det_exp(float u) {
-    if (!(u > -87.0f)) return 0.0f;
-    float n = rintf(u * 1.44269504088896341f);
-    float r = fmaf(-n, 0.693145751953125f, u);
-    r = fmaf(-n, 1.42860682030941723212e-6f, r);
-    float p = 1.0f / 5040.0f;
-    p = fmaf(p, r, 1.0f / 720.0f);
-    p = fmaf(p, r, 1.0f / 120.0f);
-    p = fmaf(p, r, 1.0f / 24.0f);
-    p = fmaf(p, r, 1.0f / 6.0f);
-    p = fmaf(p, r, 0.5f);
-    p = fmaf(p, r, 1.0f);
-    p = fmaf(p, r, 1.0f);
-    int e = (int)n;
-    return p * __int_as_float((e + 127) << 23);
-}
+// exp(u): shared IEEE-only sequence (include/egr_detmath.h), bit-identical to the oracle's.
+__device__ __forceinline__ float det_exp(float u) { return egr_det_exp(u); }
 __device__ __forceinline__ float det_pow(float d, float p) {
     if (p == 3.0f) return (d * d) * d;  // the reference's default exp_power; same left-to-right product as below
     int ip = (int)p;
@@ -199,7 +194,7 @@ __device__ __forceinline__ float det_pow(float d, float p) {
         for (int i = 1; i < ip; ++i) r = r * d;
         return r;
     }
-    return powf(d, p);
+    return egr_det_pow(d, p);
 }
 
 // RNG, integer exact (reference: csrc/utils/random.h:34-62)

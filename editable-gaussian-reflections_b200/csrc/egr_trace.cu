@@ -294,7 +294,9 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
         const uint32_t px = pix % W, py = pix / W;
         seed = tea4(pix, *c.p.metadata.total_num_calls);  // shaders.cu:88
         // camera.h:17-36
-        float view_size = tanf(*c.p.camera.vertical_fov_radians / 2);
+        float vs_, vc_;
+        egr_det_sincos(*c.p.camera.vertical_fov_radians / 2, &vs_, &vc_);
+        float view_size = vs_ / vc_;  // tan(fov/2)
         float aspect = (float)W / (float)H;
         float fx = (float)px, fy = (float)py;
         if (*cfg.jitter_primary_rays) {
@@ -307,7 +309,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
         const float *r = c.p.camera.rotation_w2c;
         f3 w0 = mk3(r[0], r[1], r[2]), w1 = mk3(r[3], r[4], r[5]), w2 = mk3(r[6], r[7], r[8]);
         o = mk3(c.p.camera.origin[0], c.p.camera.origin[1], c.p.camera.origin[2]);
-        d = normalize3(w0 * x + w1 * y - w2);
+        d = norm3c(fma3(w1, y, w0 * x) - w2);
     } else {
         // dense warps over the compacted list of rays spawned by the previous step
         const uint32_t cnt = c.ray_count[step];
@@ -440,11 +442,11 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
                     const float4 a2 = __ldg(&c.bvh.appearance[3 * (size_t)j + 2]);
                     const float nextT = T * (1.0f - h.alpha);  // forward_pass.cu:108-115
                     const float wt = T - nextT;
-                    c_rgb = c_rgb + mk3(a0.x, a0.y, a0.z) * wt;
-                    c_n = c_n + mk3(a1.x, a1.y, a1.z) * wt;
-                    c_f0 = c_f0 + mk3(a2.x, a2.y, a2.z) * wt;
-                    c_rough += a0.w * wt;
-                    c_depth += t * wt;
+                    c_rgb = fma3(mk3(a0.x, a0.y, a0.z), wt, c_rgb);
+                    c_n = fma3(mk3(a1.x, a1.y, a1.z), wt, c_n);
+                    c_f0 = fma3(mk3(a2.x, a2.y, a2.z), wt, c_f0);
+                    c_rough = fmaf(a0.w, wt, c_rough);
+                    c_depth = fmaf(t, wt, c_depth);
                     T = nextT;
                     if (chunk) chunk[i * 32 + lane] = make_float4(__uint_as_float(j), t, h.alpha, T);
                     nh++;
@@ -471,15 +473,15 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
         const float rem_T = T - T_full;
         const float nrm = fmaxf(1.0f - T, *cfg.eps_forward_normalization);
         f3 rem_rgb = div_s(c_rgb, nrm);
-        f3 o_rgb = c_rgb + rem_T * rem_rgb;
+        f3 o_rgb = fma3(rem_rgb, rem_T, c_rgb);
         float rem_depth = c_depth / nrm;
-        float o_depth = c_depth + rem_T * rem_depth;
+        float o_depth = fmaf(rem_T, rem_depth, c_depth);
         f3 rem_n = div_s(c_n, nrm);
-        f3 o_n = c_n + rem_T * rem_n;
+        f3 o_n = fma3(rem_n, rem_T, c_n);
         f3 rem_f0 = div_s(c_f0, nrm);
-        f3 o_f0 = c_f0 + rem_T * rem_f0;
+        f3 o_f0 = fma3(rem_f0, rem_T, c_f0);
         float rem_rough = c_rough / nrm;
-        float o_rough = c_rough + rem_T * rem_rough;
+        float o_rough = fmaf(rem_T, rem_rough, c_rough);
 
         f3 thr_prev = mk3(1, 1, 1);
         if (step > 0) {  // shaders.cu:112-114
@@ -517,46 +519,46 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
         uint32_t exec_code = (uint32_t)(step + 1);
         f3 thr = mk3(1, 1, 1), next_o = mk3(0, 0, 0), next_d = mk3(0, 0, 0);
         const f3 un = o_n;
-        if (!(length3(un) < *cfg.reflection_invalid_normal_threshold)) {
-            const f3 en = normalize3(un);
+        if (!(sqrtf(dot3(un, un)) < *cfg.reflection_invalid_normal_threshold)) {
+            const f3 en = norm3c(un);
             const float er = fmaxf(o_rough, *cfg.eps_min_roughness);
-            const f3 epos = o + o_depth * d;
+            const f3 epos = fma3(d, o_depth, o);
             const float u1 = rnd01(seed);
             const float u2 = rnd01(seed);
             const f3 V = -d;
-            // sample_cook_torrance (ggx_brdf.h:152-168)
+            // sample_cook_torrance (ggx_brdf.h:152-168); canonical op order shared with the oracle
             const float a = er * er;
             const float phi = (float)(2.0f * 3.14159265358979323846 * (double)u1);
-            const float cosT = sqrtf((1.0f - u2) / (1.0f + (a * a - 1.0f) * u2));
+            const float cosT = sqrtf((1.0f - u2) / fmaf(a * a - 1.0f, u2, 1.0f));
             const float sinT = sqrtf(fmaf(-cosT, cosT, 1.0f));
             float sp, cp;
-            sincosf(phi, &sp, &cp);
+            egr_det_sincos(phi, &sp, &cp);
             const f3 Hl = mk3(sinT * cp, sinT * sp, cosT);
-            const f3 Tn = normalize3(cross3(en.z < 0.999f ? mk3(0, 0, 1) : mk3(1, 0, 0), en));
-            const f3 Bn = cross3(en, Tn);
-            const f3 Hh = Hl.x * Tn + Hl.y * Bn + Hl.z * en;
+            const f3 Tn = norm3c(cross3c(en.z < 0.999f ? mk3(0, 0, 1) : mk3(1, 0, 0), en));
+            const f3 Bn = cross3c(en, Tn);
+            const f3 Hh = fma3(en, Hl.z, fma3(Bn, Hl.y, Tn * Hl.x));
             const f3 inc = -V;
-            next_d = inc - 2.0f * Hh * dotp(Hh, inc);
-            next_o = epos + *cfg.eps_ray_surface_offset * next_d;
+            next_d = fma3(Hh, -2.0f * dot3(Hh, inc), inc);
+            next_o = fma3(next_d, *cfg.eps_ray_surface_offset, epos);
             // cook_torrance_weight (ggx_brdf.h:134-150)
             f3 wgt = mk3(0, 0, 0);
             if (!(o_f0.x == 0.0f && o_f0.y == 0.0f && o_f0.z == 0.0f)) {
                 const f3 L = next_d;
-                const f3 Hn = normalize3(V + L);
-                const float NdotH = fmaxf(dotp(en, Hn), 0.0f);
-                const float VdotH = fmaxf(dotp(V, Hn), 0.0f);
-                const float NdotV = fmaxf(dotp(en, V), 0.0f);
+                const f3 Hn = norm3c(V + L);
+                const float NdotH = fmaxf(dot3(en, Hn), 0.0f);
+                const float VdotH = fmaxf(dot3(V, Hn), 0.0f);
+                const float NdotV = fmaxf(dot3(en, V), 0.0f);
                 const float kk = (a * a) / 2.0f;
-                const float NdotL = fmaxf(dotp(en, L), 0.0f);
-                const float g1v = (float)(NdotV / ((double)(NdotV * (1.0f - kk) + kk) + 1e-8));
-                const float g1l = (float)(NdotL / ((double)(NdotL * (1.0f - kk) + kk) + 1e-8));
+                const float NdotL = fmaxf(dot3(en, L), 0.0f);
+                const float g1v = (float)((double)NdotV / ((double)fmaf(NdotV, 1.0f - kk, kk) + 1e-8));
+                const float g1l = (float)((double)NdotL / ((double)fmaf(NdotL, 1.0f - kk, kk) + 1e-8));
                 const float G = g1v * g1l;
                 const float pw = 1.0f - VdotH;
                 float p5 = pw * pw;
-                p5 = p5 * p5 * pw;
-                const f3 F = o_f0 + (mk3(1, 1, 1) - o_f0) * p5;
+                p5 = (p5 * p5) * pw;
+                const f3 F = fma3(mk3(1, 1, 1) - o_f0, p5, o_f0);
                 const float den = (float)((double)(NdotH * NdotV) + 1e-8);
-                wgt = div_s(F * G * VdotH, den);
+                wgt = div_s((F * G) * VdotH, den);
             }
             thr = thr_prev * wgt;
             exec_code |= 0x100u;

@@ -39,6 +39,10 @@
 #include <omp.h>
 #endif
 
+// exp / log / sin / cos as IEEE-only sequences shared with the CUDA kernels (pure arithmetic definitions; the
+// tracing algorithm below is restated independently)
+#include "../include/egr_detmath.h"
+
 namespace {
 
 struct f3 {
@@ -80,35 +84,27 @@ constexpr int BUFFER_SIZE = 16;         // flags.h:16
 constexpr int MAX_ITERATIONS = 99;      // flags.h:17
 constexpr float ROUGH_DOWNWEIGHT_POW = 3.0f;  // flags.h:12-13
 
-// ---- deterministic exp (shared definition with the CUDA kernels) ---------------------------
-inline float det_exp(float u) {
-    if (!(u > -87.0f)) return 0.0f;
-    float n = rintf(u * 1.44269504088896341f);
-    float r = fmaf(-n, 0.693145751953125f, u);          // ln2 hi (exact in 12 bits)
-    r = fmaf(-n, 1.42860682030941723212e-6f, r);        // ln2 lo
-    float p = 1.0f / 5040.0f;
-    p = fmaf(p, r, 1.0f / 720.0f);
-    p = fmaf(p, r, 1.0f / 120.0f);
-    p = fmaf(p, r, 1.0f / 24.0f);
-    p = fmaf(p, r, 1.0f / 6.0f);
-    p = fmaf(p, r, 0.5f);
-    p = fmaf(p, r, 1.0f);
-    p = fmaf(p, r, 1.0f);
-    int e = (int)n;
-    uint32_t bits = (uint32_t)(e + 127) << 23;
-    float s;
-    std::memcpy(&s, &bits, 4);
-    return p * s;
-}
-// d^p: integer p in [1,8] by left-to-right repeated multiplication, else powf
+// ---- exp / integer powers (include/egr_detmath.h) ------------------------------------------------
+inline float det_exp(float u) { return egr_det_exp(u); }
+// d^p: exp_power 3 (the reference's default) and other small integers by left-to-right products
 inline float det_pow(float d, float p) {
+    if (p == 3.0f) return (d * d) * d;
     int ip = (int)p;
     if ((float)ip == p && ip >= 1 && ip <= 8) {
         float r = d;
         for (int i = 1; i < ip; ++i) r = r * d;
         return r;
     }
-    return powf(d, p);
+    return egr_det_pow(d, p);
+}
+// canonical explicit-fma forms (same op order as the CUDA kernels, so that the bits agree)
+inline f3 fma3(f3 a, float s, f3 c) { return mk(fmaf(a.x, s, c.x), fmaf(a.y, s, c.y), fmaf(a.z, s, c.z)); }
+inline f3 cross3c(f3 a, f3 b) {
+    return mk(fmaf(a.y, b.z, -(a.z * b.y)), fmaf(a.z, b.x, -(a.x * b.z)), fmaf(a.x, b.y, -(a.y * b.x)));
+}
+inline f3 norm3c(f3 v) {
+    float inv = 1.0f / sqrtf(dot3(v, v));
+    return v * inv;
 }
 
 // ---- RNG (utils/random.h:34-62) -----------------------------------------------------------
@@ -177,6 +173,7 @@ struct OrcOverride {  // optional: trace these rays instead of the oracle's own 
     const float *ray_origin, *ray_direction;  // [S,P,3]
     const int32_t *step_executed;             // [S,P]
     const float *records;                     // [N,16] packed geometry records, layout of orc_prepare
+    const uint32_t *leaf_rank;                // [N] position of each Gaussian in the device's leaf order
 };
 
 // test hooks for the integer-exact / IEEE-only building blocks
@@ -199,21 +196,25 @@ void orc_prepare(const OrcScene *sc, const OrcConfig *cfg, float *rec) {
     const float k = 2.0f * cfg->exp_power;
 #pragma omp parallel for schedule(static)
     for (int i = 0; i < sc->n; ++i) {
-        float sigma = 1.0f / (1.0f + expf(-sc->opacity[i]));
-        float sf = sigma <= cfg->alpha_threshold ? 0.0f : powf(k * logf(sigma / cfg->alpha_threshold), 1.0f / k);
-        f3 s = mk(expf(sc->scale[3 * i]), expf(sc->scale[3 * i + 1]), expf(sc->scale[3 * i + 2]));
+        float sigma = 1.0f / (1.0f + egr_det_exp(-sc->opacity[i]));
+        float sf = sigma <= cfg->alpha_threshold
+                       ? 0.0f
+                       : egr_det_pow(k * egr_det_log(sigma / cfg->alpha_threshold), 1.0f / k);
+        f3 s = mk(egr_det_exp(sc->scale[3 * i]), egr_det_exp(sc->scale[3 * i + 1]), egr_det_exp(sc->scale[3 * i + 2]));
         f3 S = s * sf * cfg->global_scale_factor;
         float r = sc->rotation[4 * i], x = sc->rotation[4 * i + 1], y = sc->rotation[4 * i + 2],
               z = sc->rotation[4 * i + 3];
-        float norm = sqrtf(r * r + x * x + y * y + z * z);
+        float norm = sqrtf(fmaf(z, z, fmaf(y, y, fmaf(x, x, r * r))));
         r /= norm, x /= norm, y /= norm, z /= norm;
         float R[3][3] = {
-            {1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
-            {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
-            {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+            {fmaf(-2.f, fmaf(z, z, y * y), 1.f), 2.f * fmaf(x, y, -(r * z)), 2.f * fmaf(x, z, r * y)},
+            {2.f * fmaf(x, y, r * z), fmaf(-2.f, fmaf(z, z, x * x), 1.f), 2.f * fmaf(y, z, -(r * x))},
+            {2.f * fmaf(x, z, -(r * y)), 2.f * fmaf(y, z, r * x), fmaf(-2.f, fmaf(y, y, x * x), 1.f)}};
         // The reference marks an instance visible iff sf > 0 and any size > 0; with all sizes required > 0 the
         // analytic inverse W = diag(1/S) R^T exists (a zero size is a degenerate transform OptiX cannot invert).
-        bool visible = sf > 0.0f && S.x > 0.0f && S.y > 0.0f && S.z > 0.0f && std::isfinite(norm) && norm > 0.0f;
+        bool visible = sf > 0.0f && S.x > 0.0f && S.y > 0.0f && S.z > 0.0f && std::isfinite(norm) && norm > 0.0f &&
+                       std::isfinite(sc->mean[3 * i] + sc->mean[3 * i + 1] + sc->mean[3 * i + 2]) &&
+                       std::isfinite(S.x + S.y + S.z);
         float Sv[3] = {S.x, S.y, S.z};
         float *o = rec + 16 * (size_t)i;
         float rad = fmaxf(S.x, fmaxf(S.y, S.z)) * 1.001f;
@@ -231,6 +232,45 @@ void orc_prepare(const OrcScene *sc, const OrcConfig *cfg, float *rec) {
 }  // extern "C"
 
 namespace {
+
+// Morton (leaf) order of the Gaussians, as the CUDA LBVH build defines it: 63-bit code of the mean on a 2^21 grid
+// over the bounds of the finite means, stable sort (ties keep id order).  Only used to take the product of the
+// total transmittance in the same order as the device (float products do not commute bit for bit).
+inline uint64_t expand21(uint32_t v) {
+    uint64_t x = v & 0x1fffffu;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+std::vector<uint32_t> morton_rank(const float *mean, int n) {
+    float lo[3] = {3.0e38f, 3.0e38f, 3.0e38f}, hi[3] = {-3.0e38f, -3.0e38f, -3.0e38f};
+    for (int i = 0; i < n; ++i)
+        for (int c = 0; c < 3; ++c) {
+            float v = mean[3 * (size_t)i + c];
+            if (std::isfinite(v)) lo[c] = fminf(lo[c], v), hi[c] = fmaxf(hi[c], v);
+        }
+    std::vector<uint64_t> key(n);
+    for (int i = 0; i < n; ++i) {
+        uint32_t q[3];
+        for (int c = 0; c < 3; ++c) {
+            float ext = hi[c] - lo[c];
+            float v = mean[3 * (size_t)i + c];
+            float u = ext > 0.0f ? (v - lo[c]) / ext : 0.0f;
+            u = std::isfinite(u) ? fminf(fmaxf(u, 0.0f), 1.0f) : 0.0f;
+            uint32_t qq = (uint32_t)(u * 2097152.0f);
+            q[c] = qq < 2097151u ? qq : 2097151u;
+        }
+        key[i] = (expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2]);
+    }
+    std::vector<uint32_t> order(n), rank(n);
+    for (int i = 0; i < n; ++i) order[i] = (uint32_t)i;
+    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return key[a] < key[b]; });
+    for (int i = 0; i < n; ++i) rank[order[i]] = (uint32_t)i;
+    return rank;
+}
 
 struct Hit {
     float t;
@@ -300,7 +340,7 @@ struct BoundSphere {
 
 void trace_ray(
     const float *recs, const std::vector<BoundSphere> &bs, const float *normals, int n, const OrcConfig &cfg, int step,
-    f3 o, f3 d, float tmin, float tmax, RayResult &out) {
+    f3 o, f3 d, float tmin, float tmax, RayResult &out, const std::vector<uint32_t> &rank) {
     out.hits.clear();
     out.T_full = 1.0f;
     out.n_accepted = 0;
@@ -315,12 +355,15 @@ void trace_ray(
         if (dist2 > bs[i].r2) continue;
         Hit h;
         if (!candidate(recs + 16 * (size_t)i, normals, cfg, step, o, d, tmin, tmax, h)) continue;
-        out.T_full = (float)((double)out.T_full * (1.0 - (double)h.alpha));  // shaders.cu:69-71
         out.n_accepted++;
         out.hits.push_back(h);
     }
-    std::sort(out.hits.begin(), out.hits.end(), [](const Hit &a, const Hit &b) {
-        return a.t < b.t || (a.t == b.t && a.id < b.id);
+    // exact total transmittance (shaders.cu:69-71); the reference multiplies in OptiX traversal order (unspecified),
+    // here in Morton order, which is the order the CUDA walk visits leaves in
+    std::sort(out.hits.begin(), out.hits.end(), [&](const Hit &a, const Hit &b) { return rank[a.id] < rank[b.id]; });
+    for (const Hit &h : out.hits) out.T_full = (float)((double)out.T_full * (1.0 - (double)h.alpha));
+    std::sort(out.hits.begin(), out.hits.end(), [&](const Hit &a, const Hit &b) {
+        return a.t < b.t || (a.t == b.t && rank[a.id] < rank[b.id]);
     });
 }
 
@@ -376,6 +419,11 @@ void orc_render(
         bs[i].r2 = rad * rad;
     }
 
+    // leaf order: from the caller (the device's own order, e.g. after refits without a rebuild) or recomputed
+    std::vector<uint32_t> rank;
+    if (ov && ov->leaf_rank) rank.assign(ov->leaf_rank, ov->leaf_rank + n);
+    else rank = morton_rank(sc->mean, n);
+
     std::vector<double> A_rgb, A_normal, A_f0, A_rough, A_opac, A_scale, A_mean, A_rot, A_weight;
     if (grads_enabled) {
         A_rgb.assign((size_t)n * 3, 0), A_normal.assign((size_t)n * 3, 0), A_f0.assign((size_t)n * 3, 0);
@@ -398,7 +446,9 @@ void orc_render(
             const int ix = pix % width, iy = pix / width;
             uint32_t seed = tea4((uint32_t)pix, total_num_calls);  // shaders.cu:88
             // primary ray (camera.h:17-36)
-            float view_size = tanf(cam->fovy / 2);
+            float vs_, vc_;
+            egr_det_sincos(cam->fovy / 2, &vs_, &vc_);
+            float view_size = vs_ / vc_;  // tan(fov/2)
             float aspect = (float)width / (float)height;
             float fx = (float)ix, fy = (float)iy;
             if (cfg.jitter_primary_rays) {
@@ -409,7 +459,7 @@ void orc_render(
             float y = view_size * (1.0f - 2.0f * (fy + 1.0f / 2.0f) / (float)height);
             float x = aspect * view_size * (2.0f * (fx + 1.0f / 2.0f) / (float)width - 1.0f);
             f3 ray_o = cam_o;
-            f3 ray_d = normalize(w2c0 * x + w2c1 * y - w2c2);
+            f3 ray_d = norm3c(fma3(w2c1, y, w2c0 * x) - w2c2);
 
             for (int s = 0; s < S; ++s) {  // Pixel ctor, framebuffer.h:40-68
                 StepState &q = st[s];
@@ -438,7 +488,7 @@ void orc_render(
                 // ---- forward_pass (forward_pass.cu:3-156)
                 const float tmin0 = step != 0 ? 0.0f : cam->znear;
                 const float tmax = cam->zfar;
-                trace_ray(recs, bs, sc->normal, n, cfg, step, ray_o, ray_d, tmin0, tmax, rr);
+                trace_ray(recs, bs, sc->normal, n, cfg, step, ray_o, ray_d, tmin0, tmax, rr, rank);
                 q.T = 1.0f;
                 q.T_full = rr.T_full;
                 sum_accepted += rr.n_accepted;
@@ -468,11 +518,11 @@ void orc_render(
                             float c_r = fminf(fmaxf(0.0f, sc->roughness[id]), 1.0f);
                             float nextT = q.T * (1.0f - h.alpha);  // forward_pass.cu:108-115
                             float wt = q.T - nextT;
-                            q.rgb = q.rgb + c_rgb * wt;
-                            q.normal = q.normal + c_n * wt;
-                            q.f0 = q.f0 + c_f0 * wt;
-                            q.roughness += c_r * wt;
-                            q.depth += h.t * wt;
+                            q.rgb = fma3(c_rgb, wt, q.rgb);
+                            q.normal = fma3(c_n, wt, q.normal);
+                            q.f0 = fma3(c_f0, wt, q.f0);
+                            q.roughness = fmaf(c_r, wt, q.roughness);
+                            q.depth = fmaf(h.t, wt, q.depth);
                             q.T = nextT;
                             q.comp.push_back(h);
                             q.comp_T.push_back(q.T);
@@ -495,62 +545,63 @@ void orc_render(
                 float rem_T = q.T - q.T_full;
                 float nrm = fmaxf(1.0f - q.T, cfg.eps_forward_normalization);
                 q.rem_rgb = div_s(q.rgb, nrm);
-                q.rgb = q.rgb + rem_T * q.rem_rgb;
+                q.rgb = fma3(q.rem_rgb, rem_T, q.rgb);
                 q.rem_depth = q.depth / nrm;
-                q.depth = q.depth + rem_T * q.rem_depth;
+                q.depth = fmaf(rem_T, q.rem_depth, q.depth);
                 q.rem_normal = div_s(q.normal, nrm);
-                q.normal = q.normal + rem_T * q.rem_normal;
+                q.normal = fma3(q.rem_normal, rem_T, q.normal);
                 q.rem_f0 = div_s(q.f0, nrm);
-                q.f0 = q.f0 + rem_T * q.rem_f0;
+                q.f0 = fma3(q.rem_f0, rem_T, q.f0);
                 q.rem_roughness = q.roughness / nrm;
-                q.roughness = q.roughness + rem_T * q.rem_roughness;
+                q.roughness = fmaf(rem_T, q.rem_roughness, q.roughness);
 
                 if (step > 0) q.rgb = q.rgb * st[step - 1].throughput;  // shaders.cu:112-114
                 f3 un = q.normal;
-                f3 en = normalize(un);
                 float er = fmaxf(q.roughness, cfg.eps_min_roughness);
-                if (length(un) < cfg.reflection_invalid_normal_threshold) break;  // shaders.cu:123-125
-                f3 epos = ray_o + q.depth * ray_d;
-                // sample_cook_torrance (ggx_brdf.h:152-168); argument order u1 then u2
+                if (sqrtf(dot3(un, un)) < cfg.reflection_invalid_normal_threshold) break;  // shaders.cu:123-125
+                f3 en = norm3c(un);
+                f3 epos = fma3(ray_d, q.depth, ray_o);
+                // sample_cook_torrance (ggx_brdf.h:152-168); argument order u1 then u2; canonical op order shared
+                // with the CUDA kernel (explicit fmaf where nvcc would contract)
                 float u1 = rnd(seed);
                 float u2 = rnd(seed);
                 f3 V = -ray_d;
                 float a = er * er;
                 float phi = (float)(2.0f * M_PI * (double)u1);
-                float cosT = sqrtf((1.0f - u2) / (1.0f + (a * a - 1.0f) * u2));
-                float sinT = sqrtf(fmaf(-cosT, cosT, 1.0f));  // nvcc contracts 1 - c*c (ggx_brdf.h:158) into one fma
-                f3 Hl = mk(sinT * cosf(phi), sinT * sinf(phi), cosT);
-                f3 Tn = normalize(cross(en.z < 0.999f ? mk(0, 0, 1) : mk(1, 0, 0), en));
-                f3 Bn = cross(en, Tn);
-                f3 Hh = Hl.x * Tn + Hl.y * Bn + Hl.z * en;
+                float cosT = sqrtf((1.0f - u2) / fmaf(a * a - 1.0f, u2, 1.0f));
+                float sinT = sqrtf(fmaf(-cosT, cosT, 1.0f));
+                float sp, cp;
+                egr_det_sincos(phi, &sp, &cp);
+                f3 Hl = mk(sinT * cp, sinT * sp, cosT);
+                f3 Tn = norm3c(cross3c(en.z < 0.999f ? mk(0, 0, 1) : mk(1, 0, 0), en));
+                f3 Bn = cross3c(en, Tn);
+                f3 Hh = fma3(en, Hl.z, fma3(Bn, Hl.y, Tn * Hl.x));
                 f3 inc = -V;
-                f3 next_d = inc - 2.0f * Hh * dotp(Hh, inc);  // reflect(-V,H), vec_math.h:385
-                f3 next_o = epos + cfg.eps_ray_surface_offset * next_d;
+                f3 next_d = fma3(Hh, -2.0f * dot3(Hh, inc), inc);  // reflect(-V,H), vec_math.h:385
+                f3 next_o = fma3(next_d, cfg.eps_ray_surface_offset, epos);
                 f3 ef0 = q.f0;
                 if (step > 0) q.throughput = st[step - 1].throughput;
                 // cook_torrance_weight (ggx_brdf.h:134-150)
                 f3 wgt = mk(0, 0, 0);
                 if (!(ef0.x == 0.0f && ef0.y == 0.0f && ef0.z == 0.0f)) {
                     f3 L = next_d;
-                    f3 Hn = normalize(V + L);
-                    float NdotH = fmaxf(dotp(en, Hn), 0.0f);
-                    float VdotH = fmaxf(dotp(V, Hn), 0.0f);
-                    float NdotV = fmaxf(dotp(en, V), 0.0f);
-                    float al = er * er;
-                    auto G1 = [&](f3 Wv) {
-                        float NdotW = fmaxf(dotp(en, Wv), 0.0f);
-                        float kk = (al * al) / 2.0f;
-                        return (float)(NdotW / ((double)(NdotW * (1.0f - kk) + kk) + 1e-8));
-                    };
-                    float G = G1(V) * G1(L);
+                    f3 Hn = norm3c(V + L);
+                    float NdotH = fmaxf(dot3(en, Hn), 0.0f);
+                    float VdotH = fmaxf(dot3(V, Hn), 0.0f);
+                    float NdotV = fmaxf(dot3(en, V), 0.0f);
+                    float kk = (a * a) / 2.0f;
+                    float NdotL = fmaxf(dot3(en, L), 0.0f);
+                    float g1v = (float)((double)NdotV / ((double)fmaf(NdotV, 1.0f - kk, kk) + 1e-8));
+                    float g1l = (float)((double)NdotL / ((double)fmaf(NdotL, 1.0f - kk, kk) + 1e-8));
+                    float G = g1v * g1l;
                     float pw = 1.0f - VdotH;
                     float p5 = pw * pw;
-                    p5 = p5 * p5 * pw;
-                    f3 F = ef0 + (mk(1, 1, 1) - ef0) * p5;
+                    p5 = (p5 * p5) * pw;
+                    f3 F = fma3(mk(1, 1, 1) - ef0, p5, ef0);
                     // float3 / double resolves to operator/(float3, float): the denominator is rounded to
                     // float and the numerator multiplied by its reciprocal (vec_math.h:330-333)
                     float den = (float)((double)(NdotH * NdotV) + 1e-8);
-                    wgt = div_s(F * G * VdotH, den);
+                    wgt = div_s((F * G) * VdotH, den);
                 }
                 q.throughput = q.throughput * wgt;
                 ray_o = next_o, ray_d = next_d;

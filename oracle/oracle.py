@@ -100,7 +100,8 @@ class OrcHitLists(C.Structure):
 
 
 class OrcOverride(C.Structure):
-    _fields_ = [("ray_origin", _FP), ("ray_direction", _FP), ("step_executed", _IP), ("records", _FP)]
+    _fields_ = [("ray_origin", _FP), ("ray_direction", _FP), ("step_executed", _IP), ("records", _FP),
+                ("leaf_rank", _UP)]
 
 
 def build(force: bool = False) -> str:
@@ -262,6 +263,9 @@ def render(scene, cfg: OrcConfig, cam: OrcCamera, width: int, height: int, total
         if override.get("records") is not None:
             keep_o["r"] = _f32(override["records"], (n, 16))
             ov.records = _fp(keep_o["r"])
+        if override.get("leaf_rank") is not None:
+            keep_o["k"] = np.ascontiguousarray(np.asarray(override["leaf_rank"], np.uint32).reshape(n))
+            ov.leaf_rank = keep_o["k"].ctypes.data_as(_UP)
         ovp = C.byref(ov)
     pb, pe = (0, P) if pixel_range is None else pixel_range
     L.orc_render(C.byref(s), C.byref(cfg), C.byref(cam), width, height, C.c_uint32(total_num_calls), int(bool(grads)),
