@@ -404,6 +404,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
             select_batch(refill);
         }
         if (kt[0] == FLT_MAX) done = true;  // forward_pass.cu:80-83
+        if (!__any_sync(0xffffffffu, !done)) break;
         // one hit-log chunk per warp per batch (slot-major so that 32 lanes write 512 contiguous bytes)
         float4 *chunk = nullptr;
         if (grads) {
