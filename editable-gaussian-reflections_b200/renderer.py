@@ -91,6 +91,10 @@ class GaussianRaytracer:
                               ("target_roughness", target_roughness), ("target_f0", target_f0)):
                 buf = getattr(fb, name)
                 if tgt is not None:
+                    if tgt.device.type == "cpu":
+                        # host targets: DMA the contiguous CHW image, permute to HWC on the device (a strided
+                        # host-side copy would permute 36 MB per view on one CPU core first)
+                        tgt = tgt.to(buf.device, non_blocking=True)
                     buf.copy_(tgt.moveaxis(0, -1), non_blocking=True)
                 else:
                     buf.zero_()
