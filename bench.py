@@ -56,7 +56,7 @@ class ClockSampler:
         try:
             self.f = open(self.path, "w")
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+                                          "-lms", "200"], stdout=self.f, stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 
@@ -199,24 +199,30 @@ def run_ours(args):
              [("backward", _capi.EGR_PHASE_FINISH)]
     rays_dev = torch.zeros((), dtype=torch.int64, device=dev)
 
+    def new_pair():
+        return torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
     def hot_step(view_idx, events=None):
-        """refit + forward + backward of one resident view (+ the gradient all-reduce when world > 1)."""
+        """refit + forward + backward of one resident view (+ the gradient all-reduce when world > 1).
+        `events`: pre-created {phase: (start, end)} pairs recorded around every launch of this step."""
         with torch.enable_grad():
             if events is not None:
-                events.append(("refit", torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)))
-                events[-1][1].record()
+                events["refit"][0].record()
             rt.update_bvh()
             if events is not None:
-                events[-1][2].record()
+                events["refit"][1].record()
             for name, mask in phases:
                 if events is not None:
-                    events.append((name, torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)))
-                    events[-1][1].record()
+                    events[name][0].record()
                 rt.raytrace_phases(mask)
                 if events is not None:
-                    events[-1][2].record()
+                    events[name][1].record()
         if world > 1:
+            if events is not None:
+                events["allreduce"][0].record()
             distributed.allreduce_gradients(g.grad_records)
+            if events is not None:
+                events["allreduce"][1].record()
         rays_dev.add_(rt.get_stats().num_steps_per_pixel.sum())
 
     def sync():
@@ -234,18 +240,20 @@ def run_ours(args):
     rays_dev.zero_()
     # timed region: exactly K steps between one pair of events (barrier + synchronize on both sides); selecting the
     # step's view = device-to-device copies of pose and targets that are already resident in HBM
-    clock = ClockSampler(local)
-    clock.start()
+    clock = ClockSampler(local) if rank == 0 and not os.environ.get("EGR_BENCH_NOCLOCK") else None  # one sampler per job
+    if clock:
+        clock.start()
     sync()
-    ev_all = []
-    t_a, t_b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    names = ["refit"] + [n for n, _ in phases] + (["allreduce"] if world > 1 else [])
+    ev_steps = [{n: new_pair() for n in names} for _ in range(K)]  # created before the timed region
+    t_a, t_b = new_pair()
     t_a.record()
     for i in range(K):
         set_view_device(views_dev[my_views[Wm + i]])
-        hot_step(my_views[Wm + i], ev_all)
+        hot_step(my_views[Wm + i], ev_steps[i])
     t_b.record()
     sync()
-    clocks = clock.stop()
+    clocks = clock.stop() if clock else None
     total_ms = distributed.max_over_ranks(t_a.elapsed_time(t_b), dev)
     rays = rays_dev.clone()
     if world > 1:
@@ -253,8 +261,9 @@ def run_ours(args):
     rays = int(rays.item())
     value = rays / (total_ms * 1e-3) / 1e6
     per_phase = {}
-    for name, a, b in ev_all:
-        per_phase.setdefault(name, []).append(a.elapsed_time(b))
+    for evs in ev_steps:
+        for name, (a, b) in evs.items():
+            per_phase.setdefault(name, []).append(a.elapsed_time(b))
     phase_ms = {k: sum(v) / len(v) for k, v in per_phase.items()}
 
     # ---------------- roofline of the slowest kernel ----------------

@@ -129,8 +129,10 @@ __device__ __forceinline__ void traverse(
             float t0z = (A.z - o.z) * idir.z, t1z = (B.z - o.z) * idir.z;
             float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
             float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
-            tn = tn - fabsf(tn) * 4.0e-7f;
-            tf = tf + fabsf(tf) * 4.0e-7f;
+            // widen the interval by a few ulps (conservative); multiplicative so that +-inf (a zero direction
+            // component) stays inf instead of turning into inf - inf = NaN, which the min/max below would ignore
+            tn = tn * (tn >= 0.0f ? 0.9999996f : 1.0000004f);
+            tf = tf * (tf >= 0.0f ? 1.0000004f : 0.9999996f);
             float lo = PASS0 ? sc.tmin : fmaxf(sc.tmin, w);
             float hi = PASS0 || L.cnt < LIST_CAP ? sc.tmax : fminf(sc.tmax, L.maxt);
             hit = fmaxf(tn, lo) <= fminf(tf, hi);
@@ -181,8 +183,8 @@ __device__ __forceinline__ void traverse_lane(
                 float t0z = (A.z - o.z) * idir.z, t1z = (B.z - o.z) * idir.z;
                 float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
                 float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
-                tn = tn - fabsf(tn) * 4.0e-7f;
-                tf = tf + fabsf(tf) * 4.0e-7f;
+                tn = tn * (tn >= 0.0f ? 0.9999996f : 1.0000004f);  // NaN-safe widening, see traverse()
+                tf = tf * (tf >= 0.0f ? 1.0000004f : 0.9999996f);
                 float lo = PASS0 ? sc.tmin : fmaxf(sc.tmin, w);
                 float hi = PASS0 || L.cnt < LIST_CAP ? sc.tmax : fminf(sc.tmax, L.maxt);
                 hit = fmaxf(tn, lo) <= fminf(tf, hi);
@@ -696,12 +698,16 @@ int launch_backward_impl(const TraceCtx &c, cudaStream_t st);
 
 // Blocks of k_trace_step the current device keeps resident (occupancy x SM count), capped by the hit-list scratch.
 static uint32_t resident_blocks() {
-    int dev = 0, sms = 0, per_sm = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return 1;
+    static uint32_t cached[64] = {0};  // per device; the queries take driver locks, keep them off the per-call path
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 1;
+    if (cached[dev]) return cached[dev];
+    int sms = 0, per_sm = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_step, 128, 0);
     const uint32_t nb = (uint32_t)max(1, sms * per_sm);
-    return min(nb, (uint32_t)(MAX_RESIDENT_WARPS / 4));
+    cached[dev] = min(nb, (uint32_t)(MAX_RESIDENT_WARPS / 4));
+    return cached[dev];
 }
 
 int launch_hitlog_export(const TraceCtx &c, int step, int cap, int32_t *ids, float *ts, int32_t *counts, cudaStream_t st);
