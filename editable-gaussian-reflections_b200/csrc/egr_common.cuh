@@ -128,8 +128,8 @@ __host__ __device__ inline StateLayout state_layout(uint32_t w, uint32_t h, uint
     L.warp_off = o, o = align_up(o + (size_t)L.num_warps * S * 4, 256);
     L.ray_count = o, o = align_up(o + (size_t)S * 4, 256);
     L.work_counter = o, o = align_up(o + (size_t)S * 4, 256);
-    // per-resident-warp hit lists of the forward (64 entries x 32 lanes x 8 B = 16 KiB each)
-    L.hitlist = o, o = align_up(o + (size_t)min_u32(L.num_warps + 3, MAX_RESIDENT_WARPS) * 64 * 32 * 8, 256);
+    // per-resident-warp hit lists of the forward ((64 list + 16 batch) entries x 32 lanes x 8 B = 20 KiB each)
+    L.hitlist = o, o = align_up(o + (size_t)min_u32(L.num_warps + 3, MAX_RESIDENT_WARPS) * 80 * 32 * 8, 256);
     L.total = o;
     return L;
 }

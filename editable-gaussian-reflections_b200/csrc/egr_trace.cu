@@ -282,8 +282,7 @@ __global__ void k_end(TraceCtx c) {  // raytracer.cpp:91-93 without the host syn
 
 // ---- one ray-step of one warp's 32 rays ------------------------------------------------------------------------
 __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, const int grads, const uint32_t warp,
-                                           const uint32_t lane, float *s_kt, uint32_t *s_kj, float4 *s_rec,
-                                           uint2 *list) {
+                                           const uint32_t lane, float4 *s_rec, uint2 *list) {
     const EgrConfig &cfg = c.p.config;
     const uint32_t W = c.p.image_width, H = c.p.image_height;
 
@@ -424,16 +423,20 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
                 nbatches++;
             }
         }
-        // the batch goes through shared memory so that the composite loop can index it dynamically (small code)
+        // the batch goes through memory so that the composite loop can index it dynamically (small code): 16 extra
+        // slots behind the warp's hit list (L1/L2 resident; shared memory would be carved out of the L1 the walk
+        // depends on)
+        uint2 *kspill = L.base + LIST_CAP * 32;
 #pragma unroll
-        for (int i = 0; i < KBUF; ++i) s_kt[i * 32 + lane] = kt[i], s_kj[i * 32 + lane] = kj[i];
+        for (int i = 0; i < KBUF; ++i) kspill[i * 32 + lane] = make_uint2(__float_as_uint(kt[i]), kj[i]);
         for (int i = 0; i < KBUF; ++i) {
             if (!__any_sync(0xffffffffu, !done)) break;
             if (!done) {
-                const float t = s_kt[i * 32 + lane];
+                const uint2 kq = kspill[i * 32 + lane];
+                const float t = __uint_as_float(kq.x);
                 w = fmaxf(w, t);  // forward_pass.cu:89
                 if (t < sc.tmax) {
-                    const uint32_t j = s_kj[i * 32 + lane];
+                    const uint32_t j = kq.y;
                     const float4 r0 = __ldg(&c.bvh.records[4 * (size_t)j + 0]);
                     const float4 r1 = __ldg(&c.bvh.records[4 * (size_t)j + 1]);
                     const float4 r2 = __ldg(&c.bvh.records[4 * (size_t)j + 2]);
@@ -582,20 +585,18 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
 // step 0, 32 compacted rays at a bounce step) from a counter until the step is done; a resident warp owns one hit-list
 // region for its whole life, so the lists of a step occupy a few tens of MB and stay in L2.
 __global__ void __launch_bounds__(128, 5) k_trace_step(const TraceCtx c, const int step, const int grads) {
-    __shared__ float s_kt[4][KBUF * 32];
-    __shared__ uint32_t s_kj[4][KBUF * 32];
     __shared__ float4 s_rec[4][FAT * 4];
     const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int B = min(*c.p.config.num_bounces, (int)c.S - 1);  // shaders.cu:85
     if (step > B) return;
     const uint32_t groups = step == 0 ? c.num_warps : (c.ray_count[step] + 31) / 32;
-    uint2 *list = c.hitlist + (size_t)(blockIdx.x * 4 + wib) * LIST_CAP * 32;
+    uint2 *list = c.hitlist + (size_t)(blockIdx.x * 4 + wib) * (LIST_CAP + KBUF) * 32;
     while (true) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(&c.work_counter[step], 1u);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= groups) break;
-        trace_warp(c, step, grads, g, lane, s_kt[wib], s_kj[wib], s_rec[wib], list);
+        trace_warp(c, step, grads, g, lane, s_rec[wib], list);
         __syncwarp();
     }
 }
