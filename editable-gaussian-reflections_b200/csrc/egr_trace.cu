@@ -80,10 +80,11 @@ __device__ __forceinline__ void test_candidate(
     // the accepted hit point lies on the forward ray and inside the proxy ellipsoid, hence inside its bounding
     // sphere: reject when the line misses the sphere, or when the sphere lies wholly behind the origin
     const f3 p = mk3(r0.x, r0.y, r0.z) - o;
-    const f3 cr = cross3(p, d);
-    if (!(dotp(cr, cr) <= r0.w)) return;
-    if (r0.w == 0.0f) return;  // invisible Gaussian (radius^2 = 0) that happens to sit exactly on the ray
-    if (dotp(p, d) < 0.0f && dotp(p, p) > r0.w) return;
+    const float pp = dotp(p, p), pd = dotp(p, d);
+    // squared line-sphere distance |p|^2 - (p.d)^2 <= r^2, with a slack that covers the cancellation error
+    if (!(fmaf(-pd, pd, pp) <= fmaf(2.0e-6f, pp, r0.w))) return;
+    if (r0.w == 0.0f) return;  // invisible Gaussian (radius^2 = 0)
+    if (pd < 0.0f && pp > r0.w) return;
     const float4 r1 = SHARED ? rp[1] : __ldg(rp + 1);
     const float4 r2 = SHARED ? rp[2] : __ldg(rp + 2);
     const float4 r3 = SHARED ? rp[3] : __ldg(rp + 3);

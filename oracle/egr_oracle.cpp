@@ -178,6 +178,17 @@ struct OrcOverride {  // optional: trace these rays instead of the oracle's own 
 
 // test hooks for the integer-exact / IEEE-only building blocks
 float orc_det_exp(float u) { return det_exp(u); }
+float orc_det_log(float x) { return egr_det_log(x); }
+float orc_det_sin(float x) {
+    float s_, c_;
+    egr_det_sincos(x, &s_, &c_);
+    return s_;
+}
+float orc_det_cos(float x) {
+    float s_, c_;
+    egr_det_sincos(x, &s_, &c_);
+    return c_;
+}
 uint32_t orc_tea4(uint32_t a, uint32_t b) { return tea4(a, b); }
 float orc_rnd(uint32_t *seed) { return rnd(*seed); }
 

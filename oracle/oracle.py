@@ -118,8 +118,9 @@ def lib():
         build()
         _lib = C.CDLL(_LIB_PATH)
         _lib.orc_num_threads.restype = C.c_int
-        _lib.orc_det_exp.restype = C.c_float
-        _lib.orc_det_exp.argtypes = [C.c_float]
+        for _n in ("orc_det_exp", "orc_det_log", "orc_det_sin", "orc_det_cos"):
+            getattr(_lib, _n).restype = C.c_float
+            getattr(_lib, _n).argtypes = [C.c_float]
         _lib.orc_tea4.restype = C.c_uint32
         _lib.orc_tea4.argtypes = [C.c_uint32, C.c_uint32]
         _lib.orc_rnd.restype = C.c_float

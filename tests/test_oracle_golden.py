@@ -138,6 +138,23 @@ def test_rng_known_answers(gold):
     assert seed.value == s1 and x == np.float32((s1 & 0xFFFFFF) / 16777216.0)
 
 
+def test_det_log_sincos_accuracy():
+    """include/egr_detmath.h: the shared IEEE-only log / sin / cos stay within the accuracy class of libm."""
+    L = orc.lib()
+    x = np.exp(np.linspace(-12, 12, 8001)).astype(np.float32)
+    got = np.array([L.orc_det_log(float(v)) for v in x], np.float64)
+    assert np.abs(got - np.log(x.astype(np.float64))).max() < 2e-6  # |log x| <= 12: < 3 ulp of the largest value
+    far = np.abs(np.log(x.astype(np.float64))) > 0.5
+    rel = np.abs(got[far] / np.log(x[far].astype(np.float64)) - 1)
+    assert rel.max() < 3e-7
+    a = np.linspace(-7, 7, 8001).astype(np.float32)
+    s = np.array([L.orc_det_sin(float(v)) for v in a], np.float64)
+    c = np.array([L.orc_det_cos(float(v)) for v in a], np.float64)
+    assert np.abs(s - np.sin(a.astype(np.float64))).max() < 1.5e-7
+    assert np.abs(c - np.cos(a.astype(np.float64))).max() < 1.5e-7
+    assert L.orc_det_sin(0.0) == 0.0 and L.orc_det_cos(0.0) == 1.0
+
+
 def test_det_exp_accuracy():
     L = orc.lib()
     u = np.linspace(-20, 0, 20001).astype(np.float32)
