@@ -33,6 +33,7 @@ class GaussianRaytracer:
         config.alpha_threshold.fill_(pc.cfg.alpha_threshold)
         config.exp_power.fill_(pc.cfg.exp_power)
         self.pc = pc
+        self._upload_stream = None
         self._export_param_values()
         self.cuda_module.rebuild_bvh()
 
@@ -86,21 +87,42 @@ class GaussianRaytracer:
             camera.set_pose(viewpoint_camera.camera_center.contiguous(), R_c2w_blender.contiguous())
             self._export_param_values()
             fb = self.cuda_module.get_framebuffer()
-            for name, tgt in (("target_diffuse", target_diffuse), ("target_specular", target_specular),
-                              ("target_depth", target_depth), ("target_normal", target_normal),
-                              ("target_roughness", target_roughness), ("target_f0", target_f0)):
-                buf = getattr(fb, name)
-                if tgt is not None:
-                    if tgt.device.type == "cpu":
-                        # host targets: DMA the contiguous CHW image, permute to HWC on the device (a strided
-                        # host-side copy would permute 36 MB per view on one CPU core first)
-                        tgt = tgt.to(buf.device, non_blocking=True)
-                    buf.copy_(tgt.moveaxis(0, -1), non_blocking=True)
-                else:
-                    buf.zero_()
+            tgts = (("target_diffuse", target_diffuse), ("target_specular", target_specular),
+                    ("target_depth", target_depth), ("target_normal", target_normal),
+                    ("target_roughness", target_roughness), ("target_f0", target_f0))
+            # Only the backward reads the targets (fused loss, shaders.cu:150-166), so host-resident targets are
+            # uploaded on a second stream underneath the refit and the forward launches of this call.
+            overlap = any(t is not None and t.device.type == "cpu" for _, t in tgts)
+            main = torch.cuda.current_stream()
+            if overlap:
+                if self._upload_stream is None:
+                    self._upload_stream = torch.cuda.Stream()
+                self._upload_stream.wait_stream(main)  # the previous call's backward is done with the buffers
+            with torch.cuda.stream(self._upload_stream if overlap else main):
+                for name, tgt in tgts:
+                    buf = getattr(fb, name)
+                    if tgt is not None:
+                        if tgt.device.type == "cpu":
+                            # DMA the contiguous CHW image, permute to HWC on the device (a strided host-side
+                            # copy would permute 36 MB per view on one CPU core first)
+                            tgt = tgt.to(buf.device, non_blocking=True)
+                        buf.copy_(tgt.moveaxis(0, -1), non_blocking=True)
+                    else:
+                        buf.zero_()
         if torch.is_grad_enabled() or force_update_bvh:
             self.cuda_module.update_bvh()
-        self.cuda_module.raytrace()
+        if overlap:
+            from . import _capi
+
+            S = self.cuda_module._S
+            forward = _capi.EGR_PHASE_BEGIN
+            for s in range(S):
+                forward |= _capi.EGR_PHASE_STEP(s)
+            self.cuda_module.raytrace_phases(forward)
+            main.wait_stream(self._upload_stream)
+            self.cuda_module.raytrace_phases(_capi.EGR_PHASE_FINISH)
+        else:
+            self.cuda_module.raytrace()
         if denoise:
             self.cuda_module.denoise()
         if torch.is_grad_enabled():

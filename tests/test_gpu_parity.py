@@ -337,6 +337,34 @@ def test_renderer_facade_train_like_iteration(small):
     assert float(pkg.rgb.abs().max()) > 0
 
 
+def test_renderer_facade_host_targets_overlapped_upload(small):
+    """Host-resident (pinned) targets are uploaded on a second stream under the forward; the backward must see
+    them: same gradients as with device-resident targets, twice in a row with different targets."""
+    import torch
+
+    import egr_b200
+
+    sc, cam, W, Hh = small
+    pc = scenes.SyntheticModel(sc)
+    rtr = egr_b200.GaussianRaytracer(pc, W, Hh, ppll_forward_size=1000, ppll_backward_size=4_000_000)
+    rtr.cuda_module.get_config().num_bounces.fill_(1)
+    for seed in (3, 4):
+        tg = scenes.random_targets(W, Hh, seed=seed)
+        grads = []
+        for dev, pin in (("cuda", False), ("cpu", True)):
+            view = scenes.SyntheticCamera(cam, tg, device=dev, pin=pin)
+            rtr.zero_grad()
+            for p in (pc._xyz, pc._diffuse, pc._scaling):
+                p.grad.zero_()
+            rtr.cuda_module.get_metadata().total_num_calls.zero_()
+            with torch.enable_grad():
+                egr_b200.render(view, rtr, denoise=False)
+            grads.append([p.grad.clone() for p in (pc._xyz, pc._diffuse, pc._scaling)])
+        for a, b in zip(*grads):
+            scale = float(a.abs().max())
+            assert scale > 0 and float((a - b).abs().max()) <= 1e-4 * scale
+
+
 def test_cuda_vs_committed_reference_vectors():
     """The CUDA path against tests/golden/ref_small.npz, i.e. against outputs of the reference's own shader
     sources (made by tests/golden/make_golden.py): primary-step planes <= 1e-4, RNG stream exact, and the three
