@@ -14,7 +14,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libegr_b200.so")
 SOURCES = ["egr_capi.cu", "egr_bvh.cu", "egr_trace.cu", "egr_backward.cu"]
-HEADERS = ["egr_common.cuh", "egr_trace.cuh", os.path.join("..", "..", "include", "egr_b200.h")]
+HEADERS = ["egr_common.cuh", "egr_trace.cuh", os.path.join("..", "..", "include", "egr_b200.h"),
+           os.path.join("..", "..", "include", "egr_detmath.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
     "--expt-relaxed-constexpr", "-Xcudafe", "--diag_suppress=177",

@@ -45,7 +45,6 @@ struct StepCfg {
 // unordered set in global memory (slot-major, lanes interleaved; a few tens of MB for the whole machine, L2
 // resident).  16-wide batches are selected from it; a BVH walk is repeated only when a ray has consumed all 64 and
 // is still not opaque.  Appending is one 8-byte store; only rays with more than 64 hits pay for replace-the-farthest.
-constexpr uint32_t LIST_CAP = 64;
 struct LaneList {
     uint2 *base;      // this warp's region
     uint32_t cnt;     // hits beyond the window seen by the current collection pass (may exceed LIST_CAP)
@@ -70,21 +69,24 @@ __device__ __forceinline__ void list_add(LaneList &L, const uint32_t lane, const
     L.cnt++;
 }
 
-// One candidate Gaussian against one ray: cheap conservative bounding-sphere reject, then the exact test, the
-// exact total transmittance (pass 0) and the hit list.
-template <bool PASS0, bool SHARED>
-__device__ __forceinline__ void test_candidate(
-    const BvhView &bvh, const StepCfg &sc, const float4 *rp, const float4 r0, const uint32_t leaf, const f3 o, const f3 d,
-    const float w, LaneList &L, float &T_full, int &n_acc, int &n_trav) {
-    // only the first quad r0 (centre + squared bounding radius) is needed to reject most candidates
+// One candidate Gaussian against one ray, in two parts: a cheap conservative bounding-sphere reject that needs only
+// the first record quad r0 (centre + squared bounding radius), then the exact test, the exact total transmittance
+// (pass 0) and the hit list.
+__device__ __forceinline__ bool sphere_pass(const float4 r0, const f3 o, const f3 d) {
     // the accepted hit point lies on the forward ray and inside the proxy ellipsoid, hence inside its bounding
     // sphere: reject when the line misses the sphere, or when the sphere lies wholly behind the origin
     const f3 p = mk3(r0.x, r0.y, r0.z) - o;
     const float pp = dotp(p, p), pd = dotp(p, d);
     // squared line-sphere distance |p|^2 - (p.d)^2 <= r^2, with a slack that covers the cancellation error
-    if (!(fmaf(-pd, pd, pp) <= fmaf(2.0e-6f, pp, r0.w))) return;
-    if (r0.w == 0.0f) return;  // invisible Gaussian (radius^2 = 0)
-    if (pd < 0.0f && pp > r0.w) return;
+    if (!(fmaf(-pd, pd, pp) <= fmaf(2.0e-6f, pp, r0.w))) return false;
+    if (r0.w == 0.0f) return false;  // invisible Gaussian (radius^2 = 0)
+    if (pd < 0.0f && pp > r0.w) return false;
+    return true;
+}
+template <bool PASS0, bool SHARED>
+__device__ __forceinline__ void full_test(
+    const BvhView &bvh, const StepCfg &sc, const float4 *rp, const float4 r0, const uint32_t leaf, const f3 o, const f3 d,
+    const float w, LaneList &L, float &T_full, int &n_acc, int &n_trav) {
     const float4 r1 = SHARED ? rp[1] : __ldg(rp + 1);
     const float4 r2 = SHARED ? rp[2] : __ldg(rp + 2);
     const float4 r3 = SHARED ? rp[3] : __ldg(rp + 3);
@@ -104,13 +106,15 @@ __device__ __forceinline__ void test_candidate(
         if (h.t > w) list_add(L, threadIdx.x & 31, h.t, leaf);  // strict, as forward_pass.cu:62
     }
 }
-
 // Warp-uniform stackless walk for coherent rays (the primary rays of an 8x4 tile): ONE node index per warp, every
 // lane tests its own ray against the node box.  Subtrees of at most FAT leaves are not descended: their Gaussians
 // are a contiguous range of the Morton-ordered records, which the warp stages into shared memory with one coalesced
 // load and then tests one by one from there (no dependent node loads below that level).  PASS0 visits everything
 // any lane's segment crosses (needed for the exact total transmittance); later passes only the slab (w, farthest list entry).
-constexpr uint32_t FAT = 16;
+#ifndef EGR_FAT
+#define EGR_FAT 32
+#endif
+constexpr uint32_t FAT = EGR_FAT;  // <= 32: the survivors of one range are a 32-bit mask
 template <bool PASS0>
 __device__ __forceinline__ void traverse(
     const BvhView &bvh, const StepCfg &sc, const f3 o, const f3 d, const f3 idir, const bool active, const float w,
@@ -151,9 +155,16 @@ __device__ __forceinline__ void traverse(
         __syncwarp();
         for (uint32_t q = lane; q < nl * 4; q += 32) s_rec[q] = __ldg(&bvh.records[4 * (size_t)first + q]);
         __syncwarp();
-        for (uint32_t k = 0; k < nl; ++k) {
-            if (hit)
-                test_candidate<PASS0, true>(bvh, sc, s_rec + 4 * k, s_rec[4 * k], first + k, o, d, w, L, T_full, n_acc, n_trav);
+        // sphere tests of the staged range -> this lane's survivors, then the exact tests of the survivors only
+        // (the warp runs max-over-lanes survivors instead of one body per candidate any lane accepts)
+        uint32_t pass = 0;
+        if (hit)
+            for (uint32_t k = 0; k < nl; ++k)
+                if (sphere_pass(s_rec[4 * k], o, d)) pass |= 1u << k;
+        while (pass) {
+            const uint32_t k = __ffs(pass) - 1;
+            pass &= pass - 1;
+            full_test<PASS0, true>(bvh, sc, s_rec + 4 * k, s_rec[4 * k], first + k, o, d, w, L, T_full, n_acc, n_trav);
         }
         node = skip;
     }
@@ -164,7 +175,19 @@ __device__ __forceinline__ void traverse(
 // leaves together).  The union walk above would make every lane test every node any lane needs, which is 32x
 // redundant once the rays of a warp fan out.
 constexpr uint32_t NO_LEAF = 0xFFFFFFFFu;
-constexpr uint32_t FAT_LANE = 16;
+#ifdef EGR_TASK_CLOCKS
+__shared__ uint32_t s_dbg_nodes[128], s_dbg_rounds[128];
+__shared__ long long s_dbg_tnode[4], s_dbg_tcand[4];
+#define EGR_DBG_NODE() (s_dbg_nodes[threadIdx.x]++)
+#define EGR_DBG_ROUND() (s_dbg_rounds[threadIdx.x]++)
+#else
+#define EGR_DBG_NODE()
+#define EGR_DBG_ROUND()
+#endif
+#ifndef EGR_FAT_LANE
+#define EGR_FAT_LANE 32
+#endif
+constexpr uint32_t FAT_LANE = EGR_FAT_LANE;  // <= 32: the survivors of one range are a 32-bit mask
 template <bool PASS0>
 __device__ __forceinline__ void traverse_lane(
     const BvhView &bvh, const StepCfg &sc, const f3 o, const f3 d, const f3 idir, const bool active, const float w,
@@ -173,8 +196,15 @@ __device__ __forceinline__ void traverse_lane(
     const float4 *__restrict__ nodes = bvh.nodes;
     uint32_t node = active ? 0u : end;
     while (true) {
-        uint32_t leaf = NO_LEAF, leaf_n = 0;
+        // every lane walks on until it holds TWO candidate ranges (or its walk ends): half as many warp-wide
+        // rounds, and a lane that finds its ranges early waits for fewer node visits of the others
+        uint32_t leaf = NO_LEAF, leaf_n = 0, leaf2 = NO_LEAF, leaf2_n = 0;
+#ifdef EGR_TASK_CLOCKS
+        __syncwarp();
+        const long long ta_ = clock64();
+#endif
         while (node < end) {
+            EGR_DBG_NODE();
             const float4 A = __ldg(&nodes[2 * (size_t)node]);
             const float4 B = __ldg(&nodes[2 * (size_t)node + 1]);
             bool hit = false;
@@ -196,17 +226,35 @@ __device__ __forceinline__ void traverse_lane(
             }
             const uint32_t skip = __float_as_uint(A.w), tag = __float_as_uint(B.w);
             const uint32_t nl = (skip - node + 1) >> 1;
-            if (nl <= FAT_LANE) {  // small subtree: test its (contiguous) Gaussians directly instead of descending
-                leaf = tag & ~FIRST_LEAF_FLAG;
-                leaf_n = nl;
-                node = skip;
+            if (nl > FAT_LANE) {
+                node = node + 1;
+                continue;
+            }
+            // small subtree: its Gaussians are a contiguous record range, tested directly instead of descending
+            node = skip;
+            if (leaf == NO_LEAF) {
+                leaf = tag & ~FIRST_LEAF_FLAG, leaf_n = nl;
+                continue;
+            }
+            leaf2 = tag & ~FIRST_LEAF_FLAG, leaf2_n = nl;
+            break;
+        }
+#ifdef EGR_TASK_CLOCKS
+        __syncwarp();
+        const long long tb_ = clock64();
+        if ((threadIdx.x & 31) == 0) s_dbg_tnode[threadIdx.x >> 5] += tb_ - ta_;
+#endif
+        for (int half = 0; half < 2; ++half) {
+            if (half == 1) leaf = leaf2, leaf_n = leaf2_n;
+            if (!__any_sync(0xffffffffu, leaf != NO_LEAF)) {
+                if (half == 0) return;  // no lane found anything: every walk has ended
                 break;
             }
-            node = node + 1;
-        }
-        if (!__any_sync(0xffffffffu, leaf != NO_LEAF)) break;
-        if (leaf != NO_LEAF) {
-            // the centre quads of four candidates are fetched together (independent loads), then tested
+            if (leaf == NO_LEAF) continue;
+            EGR_DBG_ROUND();
+            // part 1: the centre quads, four independent loads at a time, through the bounding-sphere test -> this
+            // lane's own set of survivors
+            uint32_t pass = 0;
             for (uint32_t k0 = 0; k0 < leaf_n; k0 += 4) {
                 float4 q[4];
 #pragma unroll
@@ -214,11 +262,21 @@ __device__ __forceinline__ void traverse_lane(
                     q[i] = k0 + i < leaf_n ? __ldg(bvh.records + 4 * (size_t)(leaf + k0 + i)) : make_float4(0, 0, 0, 0);
 #pragma unroll
                 for (int i = 0; i < 4; ++i)
-                    if (k0 + i < leaf_n)
-                        test_candidate<PASS0, false>(bvh, sc, bvh.records + 4 * (size_t)(leaf + k0 + i), q[i], leaf + k0 + i,
-                                                     o, d, w, L, T_full, n_acc, n_trav);
+                    if (k0 + i < leaf_n && sphere_pass(q[i], o, d)) pass |= 1u << (k0 + i);
+            }
+            // part 2: exact tests of the survivors only, in leaf order: the warp runs max-over-lanes survivors
+            // instead of one divergent body per candidate slot
+            while (pass) {
+                const uint32_t k = __ffs(pass) - 1;
+                pass &= pass - 1;
+                const float4 *rp = bvh.records + 4 * (size_t)(leaf + k);
+                full_test<PASS0, false>(bvh, sc, rp, __ldg(rp), leaf + k, o, d, w, L, T_full, n_acc, n_trav);
             }
         }
+#ifdef EGR_TASK_CLOCKS
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) s_dbg_tcand[threadIdx.x >> 5] += clock64() - tb_;
+#endif
     }
 }
 
@@ -597,7 +655,36 @@ __global__ void __launch_bounds__(128, 5) k_trace_step(const TraceCtx c, const i
         if (lane == 0) g = atomicAdd(&c.work_counter[step], 1u);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= groups) break;
+#ifdef EGR_TASK_CLOCKS
+        s_dbg_nodes[threadIdx.x] = 0, s_dbg_rounds[threadIdx.x] = 0;
+        if (lane == 0) s_dbg_tnode[wib] = 0, s_dbg_tcand[wib] = 0;
+        __syncwarp();
+        const long long tc0_ = clock64();
+        unsigned long long t0_;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0_));
+#endif
         trace_warp(c, step, grads, g, lane, s_rec[wib], list);
+#ifdef EGR_TASK_CLOCKS
+        {
+            unsigned long long t1_;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1_));
+            uint32_t sm_;
+            asm volatile("mov.u32 %0, %%smid;" : "=r"(sm_));
+            uint4 *dbg = (uint4 *)(c.hitlist + (size_t)3000 * (LIST_CAP + KBUF) * 32) + (size_t)step * 32768;
+            uint32_t nmax = s_dbg_nodes[threadIdx.x], nsum = nmax, rmax = s_dbg_rounds[threadIdx.x];
+            for (int o_ = 16; o_ > 0; o_ >>= 1) {
+                nmax = max(nmax, __shfl_xor_sync(0xffffffffu, nmax, o_));
+                nsum += __shfl_xor_sync(0xffffffffu, nsum, o_);
+                rmax = max(rmax, __shfl_xor_sync(0xffffffffu, rmax, o_));
+            }
+            const long long tot_ = clock64() - tc0_;
+            if (lane == 0 && g < 32768 && c.num_warps >= 4096) {
+                dbg[g] = make_uint4((uint32_t)t0_, (uint32_t)(t1_ - t0_), nmax | (rmax << 16), nsum);
+                dbg[g + 65536] = make_uint4((uint32_t)(s_dbg_tnode[wib] >> 4), (uint32_t)(s_dbg_tcand[wib] >> 4), (uint32_t)(tot_ >> 4), 0);
+            }
+            (void)sm_;
+        }
+#endif
         __syncwarp();
     }
 }

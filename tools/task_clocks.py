@@ -1,0 +1,60 @@
+import os, sys
+import numpy as np, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+import egr_b200
+from egr_b200 import scenes
+N, R = 1_000_000, 800
+dev = torch.device("cuda", 0)
+scene = scenes.kitchen_scene(N, seed=0)
+cams = scenes.kitchen_cameras(100, R, R)
+pc = scenes.SyntheticModel(scene, device=dev)
+rtr = egr_b200.GaussianRaytracer(pc, R, R, ppll_forward_size=1000, ppll_backward_size=120_000_000)
+rt = rtr.cuda_module
+tg = scenes.random_targets(R, R, seed=1)
+def pct(name, a):
+    a = a[a > 0].astype(np.float64)
+    if a.size == 0:
+        print(name, "empty"); return
+    q = np.percentile(a, [50, 90, 99, 99.9, 100])
+    print(f"{name}: n={a.size} mean={a.mean():.1f} p50={q[0]:.0f} p90={q[1]:.0f} p99={q[2]:.0f} p99.9={q[3]:.0f} max={q[4]:.0f} sum={a.sum():.3g}")
+for vi in (17,):
+    view = scenes.SyntheticCamera(cams[vi], tg, device=dev)
+    st = rt.get_stats()
+    res = {}
+    for nb in (0, 1):
+        rt.get_config().num_bounces.fill_(nb)
+        rt.get_metadata().total_num_calls.zero_()
+        with torch.enable_grad():
+            egr_b200.render(view, rtr)
+        torch.cuda.synchronize()
+        res[nb] = {k: getattr(st, k).cpu().numpy().astype(np.int64).ravel() for k in
+                   ("num_traversed_per_pixel", "num_hits_per_pixel", "num_composited_per_pixel")}
+    print("== view", vi)
+    for k in res[0]:
+        pct("step0 " + k, res[0][k]); pct("step1 " + k, res[1][k] - res[0][k])
+    ps = rt._pixel_state
+    CAPK = int(os.environ.get('LISTCAP', '64')) + 16
+    hl_bytes = 4096 * CAPK * 32 * 8
+    off = ps.numel() - ((hl_bytes + 255) // 256 * 256) + 3000 * CAPK * 32 * 8
+    dbg2 = ps[off + 65536 * 16: off + 65536 * 16 + 2 * 32768 * 16].view(torch.int32).cpu().numpy().astype(np.int64).reshape(2, 32768, 4) & 0xFFFFFFFF
+    dbg = ps[off: off + 2 * 32768 * 16].view(torch.int32).cpu().numpy().astype(np.int64).reshape(2, 32768, 4) & 0xFFFFFFFF
+    for s, ng in ((0, 20000), (1, None)):
+        d = dbg[s]
+        if ng is None:
+            ng = int((res[1]["num_traversed_per_pixel"] - res[0]["num_traversed_per_pixel"] > 0).sum() + 31) // 32
+        t0 = d[:ng, 0]; dt = d[:ng, 1]
+        t0 = np.where(t0 < t0.max() - (1 << 31), t0 + (1 << 32), t0)
+        nmax = d[:ng, 2] & 0xFFFF; rmax = d[:ng, 2] >> 16; nsum = d[:ng, 3]
+        if s == 1:
+            e = dbg2[s][:ng]
+            print(f"   cycles: node-walk {e[:,0].sum()/e[:,2].sum():.2f}  candidates {e[:,1].sum()/e[:,2].sum():.2f}  rest (select/composite/bounce) {1-(e[:,0].sum()+e[:,1].sum())/e[:,2].sum():.2f}")
+            print(f"   lane node visits per task: max-lane mean={nmax.mean():.0f} p99={np.percentile(nmax,99):.0f} max={nmax.max()}; lane-sum mean={nsum.mean():.0f}; leaf rounds max-lane mean={rmax.mean():.1f} max={rmax.max()}")
+            cc = np.corrcoef(nmax, dt)[0,1]; print(f"   corr(dur, nmax)={cc:.2f}; ns per max-lane node visit: median={np.median(dt/np.maximum(nmax,1)):.0f}")
+            order = np.argsort(-dt)[:5]
+            print("   longest:", [(int(dt[i]/1e3), int(nmax[i]), int(rmax[i]), int(nsum[i])) for i in order])
+        base = t0.min(); end = (t0 + dt).max()
+        print(f"step{s} tasks={ng} span={(end-base)/1e3:.1f}us  task dur us: mean={dt.mean()/1e3:.1f} p50={np.percentile(dt,50)/1e3:.1f} p90={np.percentile(dt,90)/1e3:.1f} p99={np.percentile(dt,99)/1e3:.1f} max={dt.max()/1e3:.1f}")
+        # how long after the last task START does the step end; and the busy fraction
+        print(f"   last start at {(t0.max()-base)/1e3:.1f}us ; sum(dur)/(span*2960 slots)={dt.sum()/((end-base)*2960):.2f}")
+        order = np.argsort(-dt)[:5]
+        print("   longest tasks (idx, start us, dur us):", [(int(i), round((t0[i]-base)/1e3,1), round(dt[i]/1e3,1)) for i in order])
