@@ -148,10 +148,9 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
                     const float4 e = __ldcs(&entries[slot * 32 + lane]);
                     const uint32_t j = __float_as_uint(e.x);
                     const float dist = e.y, alpha = e.z, Tr = e.w;
-                    const float4 r0 = __ldg(&c.bvh.records[4 * (size_t)j + 0]);
-                    const float4 r1 = __ldg(&c.bvh.records[4 * (size_t)j + 1]);
-                    const float4 r2 = __ldg(&c.bvh.records[4 * (size_t)j + 2]);
-                    const float4 r3 = __ldg(&c.bvh.records[4 * (size_t)j + 3]);
+                    float4 r0, r1, r2, r3;
+                    ldg2(&c.bvh.records[4 * (size_t)j], r0, r1);
+                    ldg2(&c.bvh.records[4 * (size_t)j + 2], r2, r3);
                     HitEval h;
                     eval_hit(r0, r1, r2, r3, o, d, tmin, tmax, exp_power, h);
                     const float sf = r1.w, sigma = r2.w;

@@ -160,6 +160,16 @@ __host__ __device__ inline f3 div_s(f3 a, float s) {
     return a * inv;
 }
 // canonical dot product of the hit-ID-critical path (mirrored by the oracle)
+#ifdef __CUDACC__
+// One 256-bit read-only load (LDG.E.256 on sm_100) of two adjacent float4: a divergent gather costs one L1 wavefront
+// per lane per instruction, so a 32-byte node / half record fetched with one instruction halves that cost.
+// `p` must be 32-byte aligned.
+__device__ __forceinline__ void ldg2(const float4 *p, float4 &a, float4 &b) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+}
+#endif
 __host__ __device__ inline float dot3(f3 a, f3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
 // canonical (explicit-fma) forms used wherever the oracle has to reproduce the bits
 __host__ __device__ inline f3 fma3(f3 a, float s, f3 c) { return mk3(fmaf(a.x, s, c.x), fmaf(a.y, s, c.y), fmaf(a.z, s, c.z)); }

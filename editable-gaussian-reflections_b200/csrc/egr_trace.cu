@@ -85,11 +85,11 @@ __device__ __forceinline__ bool sphere_pass(const float4 r0, const f3 o, const f
 }
 template <bool PASS0, bool SHARED>
 __device__ __forceinline__ void full_test(
-    const BvhView &bvh, const StepCfg &sc, const float4 *rp, const float4 r0, const uint32_t leaf, const f3 o, const f3 d,
+    const BvhView &bvh, const StepCfg &sc, const float4 *rp, const uint32_t leaf, const f3 o, const f3 d,
     const float w, LaneList &L, float &T_full, int &n_acc, int &n_trav) {
-    const float4 r1 = SHARED ? rp[1] : __ldg(rp + 1);
-    const float4 r2 = SHARED ? rp[2] : __ldg(rp + 2);
-    const float4 r3 = SHARED ? rp[3] : __ldg(rp + 3);
+    float4 r0, r1, r2, r3;
+    if (SHARED) r0 = rp[0], r1 = rp[1], r2 = rp[2], r3 = rp[3];
+    else ldg2(rp, r0, r1), ldg2(rp + 2, r2, r3);  // two 256-bit gathers (r0 was seen by the sphere test: an L1 hit)
     n_trav++;
     HitEval h;
     bool ok = eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);
@@ -124,8 +124,8 @@ __device__ __forceinline__ void traverse(
     const uint32_t lane = threadIdx.x & 31;
     uint32_t node = 0;
     while (node < end) {
-        const float4 A = __ldg(&nodes[2 * (size_t)node]);
-        const float4 B = __ldg(&nodes[2 * (size_t)node + 1]);
+        float4 A, B;
+        ldg2(&nodes[2 * (size_t)node], A, B);
         const uint32_t skip = __float_as_uint(A.w), tag = __float_as_uint(B.w);
         bool hit = false;
         if (active && A.x <= B.x) {
@@ -164,7 +164,7 @@ __device__ __forceinline__ void traverse(
         while (pass) {
             const uint32_t k = __ffs(pass) - 1;
             pass &= pass - 1;
-            full_test<PASS0, true>(bvh, sc, s_rec + 4 * k, s_rec[4 * k], first + k, o, d, w, L, T_full, n_acc, n_trav);
+            full_test<PASS0, true>(bvh, sc, s_rec + 4 * k, first + k, o, d, w, L, T_full, n_acc, n_trav);
         }
         node = skip;
     }
@@ -187,6 +187,12 @@ __shared__ long long s_dbg_tnode[4], s_dbg_tcand[4];
 #ifndef EGR_FAT_LANE
 #define EGR_FAT_LANE 32
 #endif
+#ifndef EGR_SELBATCH
+#define EGR_SELBATCH 4
+#endif
+#ifndef EGR_QBATCH
+#define EGR_QBATCH 4
+#endif
 constexpr uint32_t FAT_LANE = EGR_FAT_LANE;  // <= 32: the survivors of one range are a 32-bit mask
 template <bool PASS0>
 __device__ __forceinline__ void traverse_lane(
@@ -205,8 +211,8 @@ __device__ __forceinline__ void traverse_lane(
 #endif
         while (node < end) {
             EGR_DBG_NODE();
-            const float4 A = __ldg(&nodes[2 * (size_t)node]);
-            const float4 B = __ldg(&nodes[2 * (size_t)node + 1]);
+            float4 A, B;
+            ldg2(&nodes[2 * (size_t)node], A, B);
             bool hit = false;
             if (A.x <= B.x) {
                 float t0x = (A.x - o.x) * idir.x, t1x = (B.x - o.x) * idir.x;
@@ -252,16 +258,16 @@ __device__ __forceinline__ void traverse_lane(
             }
             if (leaf == NO_LEAF) continue;
             EGR_DBG_ROUND();
-            // part 1: the centre quads, four independent loads at a time, through the bounding-sphere test -> this
+            // part 1: the centre quads, EGR_QBATCH independent loads at a time, through the bounding-sphere test -> this
             // lane's own set of survivors
             uint32_t pass = 0;
-            for (uint32_t k0 = 0; k0 < leaf_n; k0 += 4) {
-                float4 q[4];
+            for (uint32_t k0 = 0; k0 < leaf_n; k0 += EGR_QBATCH) {
+                float4 q[EGR_QBATCH];
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
+                for (int i = 0; i < EGR_QBATCH; ++i)
                     q[i] = k0 + i < leaf_n ? __ldg(bvh.records + 4 * (size_t)(leaf + k0 + i)) : make_float4(0, 0, 0, 0);
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
+                for (int i = 0; i < EGR_QBATCH; ++i)
                     if (k0 + i < leaf_n && sphere_pass(q[i], o, d)) pass |= 1u << (k0 + i);
             }
             // part 2: exact tests of the survivors only, in leaf order: the warp runs max-over-lanes survivors
@@ -270,7 +276,7 @@ __device__ __forceinline__ void traverse_lane(
                 const uint32_t k = __ffs(pass) - 1;
                 pass &= pass - 1;
                 const float4 *rp = bvh.records + 4 * (size_t)(leaf + k);
-                full_test<PASS0, false>(bvh, sc, rp, __ldg(rp), leaf + k, o, d, w, L, T_full, n_acc, n_trav);
+                full_test<PASS0, false>(bvh, sc, rp, leaf + k, o, d, w, L, T_full, n_acc, n_trav);
             }
         }
 #ifdef EGR_TASK_CLOCKS
@@ -340,6 +346,7 @@ __global__ void k_end(TraceCtx c) {  // raytracer.cpp:91-93 without the host syn
 }
 
 // ---- one ray-step of one warp's 32 rays ------------------------------------------------------------------------
+template <bool LANE_WALK>
 __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, const int grads, const uint32_t warp,
                                            const uint32_t lane, float4 *s_rec, uint2 *list) {
     const EgrConfig &cfg = c.p.config;
@@ -408,7 +415,6 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
 
     float kt[KBUF];
     uint32_t kj[KBUF];
-    kb_reset(kt, kj);
     float T_full = 1.0f, T = 1.0f;
     int n_acc = 0, n_trav = 0, nh = 0;
     f3 c_rgb = mk3(0, 0, 0), c_n = mk3(0, 0, 0), c_f0 = mk3(0, 0, 0);
@@ -417,7 +423,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
     bool done = !alive;
 
     // primary rays of an 8x4 tile are coherent: one warp-uniform walk; bounce rays fan out: per-lane walks
-    const bool lane_walk = c.force_walk == 2 || (c.force_walk == 0 && step > 0);
+    constexpr bool lane_walk = LANE_WALK;
     LaneList L;
     L.base = list;
     list_reset(L);
@@ -439,12 +445,18 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
         const uint32_t mine = mx;
 #pragma unroll
         for (int o_ = 16; o_ > 0; o_ >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o_));
-        if (on) kb_reset(kt, kj);
-        for (uint32_t e = 0; e < mx; ++e) {
-            if (e < mine) {
-                const uint2 q = L.base[e * 32 + lane];
-                const float t = __uint_as_float(q.x);
-                if (t > w && t < kt[KBUF - 1]) kb_insert(kt, kj, t, q.y);
+        kb_reset(kt, kj);  // unconditional: the k-buffer is dead across every walk (registers)
+        // EGR_SELBATCH independent list loads in flight per iteration (the list is written with plain stores and read
+        // back from L2: one exposed latency per entry otherwise)
+        for (uint32_t e = 0; e < mx; e += EGR_SELBATCH) {
+            uint2 q[EGR_SELBATCH];
+#pragma unroll
+            for (int i = 0; i < EGR_SELBATCH; ++i)
+                q[i] = e + i < mine ? L.base[(e + i) * 32 + lane] : make_uint2(0xFF800000u, 0u);  // -inf: never selected
+#pragma unroll
+            for (int i = 0; i < EGR_SELBATCH; ++i) {
+                const float t = __uint_as_float(q[i].x);
+                if (t > w && t < kt[KBUF - 1]) kb_insert(kt, kj, t, q[i].y);
             }
         }
     };
@@ -455,13 +467,23 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
         // a batch that is not full is only final if the list holds every hit beyond the window; otherwise the ray
         // has more than LIST_CAP hits: collect the next LIST_CAP nearest with one more walk, then select again
         const bool refill = !done && kt[KBUF - 1] == FLT_MAX && L.cnt > LIST_CAP;
-        if (__any_sync(0xffffffffu, refill)) {
+        if (__any_sync(0xffffffffu, refill)) {  // rare: the batches of the other lanes wait in the spill slots
+            uint2 *kpark = L.base + LIST_CAP * 32;
+#pragma unroll
+            for (int i = 0; i < KBUF; ++i) kpark[i * 32 + lane] = make_uint2(__float_as_uint(kt[i]), kj[i]);
             if (refill) list_reset(L);
             int dummy_acc = 0;
             float dummy_T = 1.0f;
             if (lane_walk) traverse_lane<false>(c.bvh, sc, o, d, idir, refill, w, L, dummy_T, dummy_acc, n_trav);
             else traverse<false>(c.bvh, sc, o, d, idir, refill, w, L, dummy_T, dummy_acc, n_trav, s_rec);
             select_batch(refill);
+            if (!refill) {
+#pragma unroll
+                for (int i = 0; i < KBUF; ++i) {
+                    const uint2 kq = kpark[i * 32 + lane];
+                    kt[i] = __uint_as_float(kq.x), kj[i] = kq.y;
+                }
+            }
         }
         if (kt[0] == FLT_MAX) done = true;  // forward_pass.cu:80-83
         if (!__any_sync(0xffffffffu, !done)) break;
@@ -496,10 +518,9 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
                 w = fmaxf(w, t);  // forward_pass.cu:89
                 if (t < sc.tmax) {
                     const uint32_t j = kq.y;
-                    const float4 r0 = __ldg(&c.bvh.records[4 * (size_t)j + 0]);
-                    const float4 r1 = __ldg(&c.bvh.records[4 * (size_t)j + 1]);
-                    const float4 r2 = __ldg(&c.bvh.records[4 * (size_t)j + 2]);
-                    const float4 r3 = __ldg(&c.bvh.records[4 * (size_t)j + 3]);
+                    float4 r0, r1, r2, r3;
+                    ldg2(&c.bvh.records[4 * (size_t)j], r0, r1);
+                    ldg2(&c.bvh.records[4 * (size_t)j + 2], r2, r3);
                     HitEval h;
                     eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);  // same bits as in the walk
                     const float4 a0 = __ldg(&c.bvh.appearance[3 * (size_t)j + 0]);
@@ -643,6 +664,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
 // Persistent launch: as many blocks as fit on the machine, every warp fetches the next 32-ray group (an 8x4 tile at
 // step 0, 32 compacted rays at a bounce step) from a counter until the step is done; a resident warp owns one hit-list
 // region for its whole life, so the lists of a step occupy a few tens of MB and stay in L2.
+template <bool LANE_WALK>
 __global__ void __launch_bounds__(128, 5) k_trace_step(const TraceCtx c, const int step, const int grads) {
     __shared__ float4 s_rec[4][FAT * 4];
     const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -663,7 +685,7 @@ __global__ void __launch_bounds__(128, 5) k_trace_step(const TraceCtx c, const i
         unsigned long long t0_;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0_));
 #endif
-        trace_warp(c, step, grads, g, lane, s_rec[wib], list);
+        trace_warp<LANE_WALK>(c, step, grads, g, lane, s_rec[wib], list);
 #ifdef EGR_TASK_CLOCKS
         {
             unsigned long long t1_;
@@ -793,7 +815,10 @@ static uint32_t resident_blocks() {
     if (cached[dev]) return cached[dev];
     int sms = 0, per_sm = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_step, 128, 0);
+    int per_sm_lane = 0;
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_step<false>, 128, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_lane, k_trace_step<true>, 128, 0);
+    per_sm = max(per_sm, per_sm_lane);
     const uint32_t nb = (uint32_t)max(1, sms * per_sm);
     cached[dev] = min(nb, (uint32_t)(MAX_RESIDENT_WARPS / 4));
     return cached[dev];
@@ -833,7 +858,10 @@ extern "C" int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32
     for (uint32_t s = 0; s < c.S; ++s)
         if (phase_mask & EGR_PHASE_STEP(s)) {
             if (s > 0) k_scan_spawned<<<1, 1024, 0, st>>>(c, (int)s);
-            k_trace_step<<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
+            // primary rays of an 8x4 tile are coherent: warp-uniform walk; bounce rays fan out: per-lane walks
+            const bool lane_walk = c.force_walk == 2 || (c.force_walk == 0 && s > 0);
+            if (lane_walk) k_trace_step<true><<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
+            else k_trace_step<false><<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
         }
     if (phase_mask & EGR_PHASE_FINISH) {
         if (grads_enabled) {
