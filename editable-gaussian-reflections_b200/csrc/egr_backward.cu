@@ -137,20 +137,25 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
             const char *base = (const char *)c.p.hitlog + (size_t)chunk * HITLOG_CHUNK_BYTES;
             const float4 *entries = (const float4 *)(base + 128);
             const uint32_t prev = *(const uint32_t *)base;
+            // the log entry of the next slot is fetched one iteration ahead (coalesced, streamed once from HBM)
+            float4 e_next = (b * KBUF + KBUF - 1) < nh ? __ldcs(&entries[(KBUF - 1) * 32 + lane]) : make_float4(0, 0, 0, 0);
             for (int slot = KBUF - 1; slot >= 0; --slot) {
                 const bool has = (b * KBUF + slot) < nh;
+                const float4 e = e_next;
+                if (slot > 0 && (b * KBUF + slot - 1) < nh) e_next = __ldcs(&entries[(slot - 1) * 32 + lane]);
                 if (!__any_sync(0xffffffffu, has)) continue;
                 float g[24];
 #pragma unroll
                 for (int k = 0; k < 24; ++k) g[k] = 0.0f;
                 uint32_t id = 0;
                 if (has) {
-                    const float4 e = __ldcs(&entries[slot * 32 + lane]);
                     const uint32_t j = __float_as_uint(e.x);
                     const float dist = e.y, alpha = e.z, Tr = e.w;
                     float4 r0, r1, r2, r3;
                     ldg2(&c.bvh.records[4 * (size_t)j], r0, r1);
                     ldg2(&c.bvh.records[4 * (size_t)j + 2], r2, r3);
+                    float4 q4, s4;  // raw quaternion, raw log-scale as of the last refit (same values as the tensors)
+                    ldg2(&c.bvh.rawgeo[2 * (size_t)j], q4, s4);
                     HitEval h;
                     eval_hit(r0, r1, r2, r3, o, d, tmin, tmax, exp_power, h);
                     const float sf = r1.w, sigma = r2.w;
@@ -203,9 +208,7 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
                                    sf;
                     const f3 l0 = -dxw.x * h.x, l1 = -dxw.y * h.x, l2 = -dxw.z * h.x;
                     // scale / rotation (backward_pass.cu:169-207) from the raw parameters
-                    const f3 sraw = ld3(gs.scale, id);
-                    const f3 sc_e = mk3(expf(sraw.x), expf(sraw.y), expf(sraw.z));
-                    const float4 q4 = __ldg(&reinterpret_cast<const float4 *>(gs.rotation)[id]);
+                    const f3 sc_e = mk3(expf(s4.x), expf(s4.y), expf(s4.z));
                     const float qn = sqrtf(q4.x * q4.x + q4.y * q4.y + q4.z * q4.z + q4.w * q4.w);
                     const float iqn = 1.0f / qn;
                     const float r = q4.x * iqn, xq = q4.y * iqn, yq = q4.z * iqn, zq = q4.w * iqn;

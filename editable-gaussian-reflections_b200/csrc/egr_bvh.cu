@@ -202,8 +202,8 @@ __global__ void __launch_bounds__(256) k_refit(BvhView bvh, EgrGaussians g, EgrC
     // CPU oracle reproduces these records bit for bit
     float sigma = 1.0f / (1.0f + egr_det_exp(-g.opacity[id]));
     float sf = sigma <= alpha_threshold ? 0.0f : egr_det_pow(k * egr_det_log(sigma / alpha_threshold), 1.0f / k);
-    f3 s = mk3(egr_det_exp(g.scale[3 * (size_t)id]), egr_det_exp(g.scale[3 * (size_t)id + 1]),
-               egr_det_exp(g.scale[3 * (size_t)id + 2]));
+    const f3 sraw = ld3(g.scale, id);
+    f3 s = mk3(egr_det_exp(sraw.x), egr_det_exp(sraw.y), egr_det_exp(sraw.z));
     f3 S = s * sf * gsf;
     const float4 q4 = reinterpret_cast<const float4 *>(g.rotation)[id];
     float r = q4.x, x = q4.y, y = q4.z, z = q4.w;
@@ -229,6 +229,9 @@ __global__ void __launch_bounds__(256) k_refit(BvhView bvh, EgrGaussians g, EgrC
     bvh.records[4 * (size_t)j + 1] = make_float4(Wr[0][0], Wr[0][1], Wr[0][2], sf);
     bvh.records[4 * (size_t)j + 2] = make_float4(Wr[1][0], Wr[1][1], Wr[1][2], sigma);
     bvh.records[4 * (size_t)j + 3] = make_float4(Wr[2][0], Wr[2][1], Wr[2][2], __uint_as_float(id));
+    // raw parameters the backward differentiates through, in leaf order next to the record (one dependent gather less)
+    bvh.rawgeo[2 * (size_t)j + 0] = q4;
+    bvh.rawgeo[2 * (size_t)j + 1] = make_float4(sraw.x, sraw.y, sraw.z, 0.0f);
 
     // world box of the image of [-1,1]^3 under M = R diag(S), inflated so that it is strictly conservative w.r.t.
     // the exact local-space test (which alone defines the candidate set)

@@ -36,7 +36,7 @@ __host__ __device__ inline size_t align_up(size_t v, size_t a) { return (v + a -
 // left child of an internal node is node+1 and `skip` is the first node after the subtree, which makes the
 // traversal stackless (one index per warp).
 struct BvhLayout {
-    size_t sorted_ids, records, appearance, nodes, parents, leaf_node, flags, bounds, total;
+    size_t sorted_ids, records, rawgeo, appearance, nodes, parents, leaf_node, flags, bounds, total;
     uint32_t n, num_nodes;
 };
 __host__ __device__ inline BvhLayout bvh_layout(uint32_t n) {
@@ -47,6 +47,7 @@ __host__ __device__ inline BvhLayout bvh_layout(uint32_t n) {
     L.bounds = o, o = align_up(o + 64, 256);
     L.sorted_ids = o, o = align_up(o + (size_t)n * 4, 256);
     L.records = o, o = align_up(o + (size_t)n * 64, 256);
+    L.rawgeo = o, o = align_up(o + (size_t)n * 32, 256);
     L.appearance = o, o = align_up(o + (size_t)n * 48, 256);
     L.nodes = o, o = align_up(o + (size_t)L.num_nodes * 32, 256);
     L.parents = o, o = align_up(o + (size_t)L.num_nodes * 4, 256);
@@ -60,6 +61,7 @@ struct BvhView {
     float *bounds;          // [6] scene bounds of the means (min xyz, max xyz) used for the Morton grid
     uint32_t *sorted_ids;   // [n] leaf j -> Gaussian id
     float4 *records;        // [n][4] geometry record in leaf order (layout: eval_hit below)
+    float4 *rawgeo;         // [n][2] raw quaternion | raw log-scale,_ in leaf order (the backward's second gather by leaf)
     float4 *appearance;     // [n][3] activated rgb,rough | normal,_ | f0,_
     float4 *nodes;          // [num_nodes][2]: (bmin.xyz, skip) (bmax.xyz, leaf | FIRST_LEAF_FLAG+first leaf)
     uint32_t *parents;      // [num_nodes] preorder index of the parent
@@ -74,6 +76,7 @@ inline BvhView bvh_view(void *storage, uint32_t n) {
     v.bounds = (float *)(b + L.bounds);
     v.sorted_ids = (uint32_t *)(b + L.sorted_ids);
     v.records = (float4 *)(b + L.records);
+    v.rawgeo = (float4 *)(b + L.rawgeo);
     v.appearance = (float4 *)(b + L.appearance);
     v.nodes = (float4 *)(b + L.nodes);
     v.parents = (uint32_t *)(b + L.parents);

@@ -55,7 +55,7 @@ def test_size_queries_and_argument_errors_without_gpu():
     lib = _capi.load()
     assert lib.egr_bvh_storage_bytes(0) < lib.egr_bvh_storage_bytes(1) < lib.egr_bvh_storage_bytes(1000)
     per = (lib.egr_bvh_storage_bytes(2_000_000) - lib.egr_bvh_storage_bytes(1_000_000)) / 1e6
-    assert 64 + 48 + 64 + 4 * 4 <= per <= 220  # records + appearance + 2 nodes + index arrays per Gaussian
+    assert 64 + 32 + 48 + 64 + 4 * 4 <= per <= 240  # records + raw geometry + appearance + 2 nodes + index arrays per Gaussian
     assert lib.egr_pixel_state_bytes(800, 800, 3) >= 40 * 3 * 640000 * 4
     assert lib.egr_hitlog_bytes_for_hits(512) == 128 + 16 * 32 * 16
     assert lib.egr_raytrace(None, 0, None) == -1 and b"null" in lib.egr_last_error()
