@@ -291,9 +291,11 @@ int launch_hitlog_export(const TraceCtx &c, int step, int cap, int32_t *ids, flo
     return EGR_OK;
 }
 
-int launch_backward_impl(const TraceCtx &c, cudaStream_t st) {
+// Backward of the steps in `step_mask` (bit s = step s), last step first (shaders.cu:157).
+int launch_backward_impl(const TraceCtx &c, uint32_t step_mask, cudaStream_t st) {
     const uint32_t blocks = (c.num_warps + 3) / 4;
-    for (int step = (int)c.S - 1; step >= 0; --step) k_backward<<<blocks, 128, 0, st>>>(c, step);
+    for (int step = (int)c.S - 1; step >= 0; --step)
+        if (step_mask >> step & 1u) k_backward<<<blocks, 128, 0, st>>>(c, step);
     EGR_CUDA_TRY(cudaGetLastError());
     return EGR_OK;
 }

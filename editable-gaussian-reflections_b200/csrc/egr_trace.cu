@@ -9,6 +9,8 @@
 #include <float.h>
 #include <stdlib.h>
 
+#include <mutex>
+
 #include "egr_trace.cuh"
 
 namespace egr {
@@ -664,14 +666,16 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
 // Persistent launch: as many blocks as fit on the machine, every warp fetches the next 32-ray group (an 8x4 tile at
 // step 0, 32 compacted rays at a bounce step) from a counter until the step is done; a resident warp owns one hit-list
 // region for its whole life, so the lists of a step occupy a few tens of MB and stay in L2.
-template <bool LANE_WALK>
-__global__ void __launch_bounds__(128, 5) k_trace_step(const TraceCtx c, const int step, const int grads) {
-    __shared__ float4 s_rec[4][FAT * 4];
+// The bounce launch uses one-warp blocks: a block's registers are released as soon as its own warp runs out of work,
+// which lets the blocks of the overlapped backward in while the long tasks of the bounce step drain.
+template <bool LANE_WALK, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS, 20 / WARPS) k_trace_step(const TraceCtx c, const int step, const int grads) {
+    __shared__ float4 s_rec[LANE_WALK ? 1 : WARPS][LANE_WALK ? 1 : FAT * 4];
     const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int B = min(*c.p.config.num_bounces, (int)c.S - 1);  // shaders.cu:85
     if (step > B) return;
     const uint32_t groups = step == 0 ? c.num_warps : (c.ray_count[step] + 31) / 32;
-    uint2 *list = c.hitlist + (size_t)(blockIdx.x * 4 + wib) * (LIST_CAP + KBUF) * 32;
+    uint2 *list = c.hitlist + (size_t)(blockIdx.x * WARPS + wib) * (LIST_CAP + KBUF) * 32;
     while (true) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(&c.work_counter[step], 1u);
@@ -685,7 +689,7 @@ __global__ void __launch_bounds__(128, 5) k_trace_step(const TraceCtx c, const i
         unsigned long long t0_;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0_));
 #endif
-        trace_warp<LANE_WALK>(c, step, grads, g, lane, s_rec[wib], list);
+        trace_warp<LANE_WALK>(c, step, grads, g, lane, s_rec[LANE_WALK ? 0 : wib], list);
 #ifdef EGR_TASK_CLOCKS
         {
             unsigned long long t1_;
@@ -805,7 +809,7 @@ static int make_ctx(const EgrParams *p, TraceCtx &c) {
     return EGR_OK;
 }
 
-int launch_backward_impl(const TraceCtx &c, cudaStream_t st);
+int launch_backward_impl(const TraceCtx &c, uint32_t step_mask, cudaStream_t st);
 
 // Blocks of k_trace_step the current device keeps resident (occupancy x SM count), capped by the hit-list scratch.
 static uint32_t resident_blocks() {
@@ -816,12 +820,40 @@ static uint32_t resident_blocks() {
     int sms = 0, per_sm = 0;
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     int per_sm_lane = 0;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_step<false>, 128, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_lane, k_trace_step<true>, 128, 0);
-    per_sm = max(per_sm, per_sm_lane);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_step<false, 4>, 128, 0);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_lane, k_trace_step<true, 1>, 32, 0);
+    per_sm = min(per_sm, per_sm_lane / 4);  // both launches use the same number of resident warps (hit-list regions)
     const uint32_t nb = (uint32_t)max(1, sms * per_sm);
     cached[dev] = min(nb, (uint32_t)(MAX_RESIDENT_WARPS / 4));
     return cached[dev];
+}
+
+// Second stream of a device, on which the backward of step s-1 runs underneath the forward of step s (the bounce
+// forward is a few thousand long latency-bound warp tasks that leave most of the machine idle while they drain).
+// Created at the first grad-mode call on the device; never destroyed.
+struct SideStream {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+    std::mutex order;  // record + wait of a shared event must not interleave between host threads
+    int state = 0;  // 0 = not tried, 1 = ready, -1 = unavailable (creation failed: the tracer runs serially)
+};
+static SideStream *side_stream() {
+    static SideStream per_dev[64];
+    static std::mutex mu;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    SideStream &s = per_dev[dev];
+    if (s.state == 0) {
+        const char *e = getenv("EGR_NO_OVERLAP");
+        bool ok = !(e && atoi(e) != 0);
+        ok = ok && cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) == cudaSuccess;
+        ok = ok && cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming) == cudaSuccess;
+        ok = ok && cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming) == cudaSuccess;
+        if (!ok) cudaGetLastError();
+        s.state = ok ? 1 : -1;
+    }
+    return s.state == 1 ? &s : nullptr;
 }
 
 int launch_hitlog_export(const TraceCtx &c, int step, int cap, int32_t *ids, float *ts, int32_t *counts, cudaStream_t st);
@@ -855,18 +887,41 @@ extern "C" int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32
         k_begin<<<(c.P + 255) / 256, 256, 0, st>>>(c, grads_enabled);
     }
     const uint32_t blocks = min((c.num_warps + 3) / 4, resident_blocks());
+    // Within ONE call that holds the forward of step 1 and FINISH, the backward of step 0 is forked onto the
+    // device's side stream just before the forward of step 1 is launched: the primary step's loss gradient uses only
+    // its own planes (diffuse/depth/normal/f0/roughness of step 0, backward_pass.cu:81-99) and gradient sums are
+    // atomics.  The bounce steps share one loss on the SUM of their radiance (backward_pass.cu:101-108), so their
+    // backward has to wait for the last forward.
+    const bool finish = (phase_mask & EGR_PHASE_FINISH) != 0;
+    SideStream *side = grads_enabled && finish && c.S > 1 ? side_stream() : nullptr;
+    uint32_t forked = 0;
     for (uint32_t s = 0; s < c.S; ++s)
         if (phase_mask & EGR_PHASE_STEP(s)) {
+            if (side && s == 1) {  // the forward of step 0 precedes this launch in stream order (same or earlier call)
+                {
+                    std::lock_guard<std::mutex> lock(side->order);
+                    EGR_CUDA_TRY(cudaEventRecord(side->fork, st));
+                    EGR_CUDA_TRY(cudaStreamWaitEvent(side->stream, side->fork, 0));
+                }
+                rc = launch_backward_impl(c, 1u << (s - 1), side->stream);
+                if (rc) return rc;
+                forked |= 1u << (s - 1);
+            }
             if (s > 0) k_scan_spawned<<<1, 1024, 0, st>>>(c, (int)s);
             // primary rays of an 8x4 tile are coherent: warp-uniform walk; bounce rays fan out: per-lane walks
             const bool lane_walk = c.force_walk == 2 || (c.force_walk == 0 && s > 0);
-            if (lane_walk) k_trace_step<true><<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
-            else k_trace_step<false><<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
+            if (lane_walk) k_trace_step<true, 1><<<blocks * 4, 32, 0, st>>>(c, (int)s, grads_enabled);
+            else k_trace_step<false, 4><<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
         }
     if (phase_mask & EGR_PHASE_FINISH) {
         if (grads_enabled) {
-            rc = launch_backward_impl(c, st);
+            rc = launch_backward_impl(c, ~forked, st);
             if (rc) return rc;
+            if (forked) {
+                std::lock_guard<std::mutex> lock(side->order);
+                EGR_CUDA_TRY(cudaEventRecord(side->join, side->stream));
+                EGR_CUDA_TRY(cudaStreamWaitEvent(st, side->join, 0));
+            }
         } else {
             k_resolve<<<(c.P + 255) / 256, 256, 0, st>>>(c);
         }

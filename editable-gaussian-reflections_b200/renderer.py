@@ -114,13 +114,15 @@ class GaussianRaytracer:
         if overlap:
             from . import _capi
 
+            # primary step first; the rest of the call (bounce steps + backward, which the library overlaps among
+            # themselves) needs the targets
             S = self.cuda_module._S
-            forward = _capi.EGR_PHASE_BEGIN
-            for s in range(S):
-                forward |= _capi.EGR_PHASE_STEP(s)
-            self.cuda_module.raytrace_phases(forward)
+            rest = _capi.EGR_PHASE_FINISH
+            for s in range(1, S):
+                rest |= _capi.EGR_PHASE_STEP(s)
+            self.cuda_module.raytrace_phases(_capi.EGR_PHASE_BEGIN | _capi.EGR_PHASE_STEP(0))
             main.wait_stream(self._upload_stream)
-            self.cuda_module.raytrace_phases(_capi.EGR_PHASE_FINISH)
+            self.cuda_module.raytrace_phases(rest)
         else:
             self.cuda_module.raytrace()
         if denoise:

@@ -365,6 +365,37 @@ def test_renderer_facade_host_targets_overlapped_upload(small):
             assert scale > 0 and float((a - b).abs().max()) <= 1e-4 * scale
 
 
+def test_overlapped_backward_equals_serial_backward(small):
+    """One raytrace() call runs the backward of step s-1 on a side stream under the forward of step s; the same
+    launches issued one call at a time run serially.  Same gradients (float atomics: order-level differences)."""
+    import torch
+
+    from egr_b200 import _capi
+
+    sc, cam, W, Hh = small
+    cfg = dict(num_bounces=2, jitter_primary_rays=True, loss_weight_diffuse=5.0, loss_weight_specular=3.0,
+               loss_weight_depth=2.5, loss_weight_normal=2.5)
+    rt = H.make_gpu_raytracer(sc, cam, cfg)
+    H.set_targets(rt, scenes.random_targets(W, Hh, seed=5))
+    g = rt.get_gaussians()
+    res = []
+    for mode in ("one_call", "serial", "one_call"):
+        g.grad_records.zero_()
+        rt.get_metadata().total_num_calls.zero_()
+        with torch.enable_grad():
+            if mode == "one_call":
+                rt.raytrace()
+            else:
+                for mask in [_capi.EGR_PHASE_BEGIN] + [_capi.EGR_PHASE_STEP(s) for s in range(3)] + [_capi.EGR_PHASE_FINISH]:
+                    rt.raytrace_phases(mask)
+        torch.cuda.synchronize()
+        res.append(g.grad_records.clone())
+    scale = res[1].abs().amax(dim=0).clamp_min(1e-20)
+    for r in (res[0], res[2]):
+        assert float(((r - res[1]).abs() / scale).max()) <= 1e-4
+    assert float(res[1].abs().max()) > 0
+
+
 def test_cuda_vs_committed_reference_vectors():
     """The CUDA path against tests/golden/ref_small.npz, i.e. against outputs of the reference's own shader
     sources (made by tests/golden/make_golden.py): primary-step planes <= 1e-4, RNG stream exact, and the three
