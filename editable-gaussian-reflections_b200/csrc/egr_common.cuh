@@ -111,6 +111,11 @@ enum StatePlane {
 #define EGR_LIST_CAP 128
 #endif
 constexpr uint32_t LIST_CAP = EGR_LIST_CAP;  // per-ray hit list: the LIST_CAP nearest hits beyond the window (egr_trace.cu)
+// One hit-list region per resident warp of the forward launch, lanes interleaved: LIST_CAP rows of 32 distances
+// (scanned by the batch selection), LIST_CAP rows of 32 (leaf, alpha) pairs (gathered once per selected hit), and
+// KBUF rows of 32 (t, leaf, alpha, -) for the selected batch.
+constexpr size_t HITLIST_T_BYTES = (size_t)LIST_CAP * 32 * 4, HITLIST_LA_BYTES = (size_t)LIST_CAP * 32 * 8;
+constexpr size_t HITLIST_WARP_BYTES = HITLIST_T_BYTES + HITLIST_LA_BYTES + (size_t)KBUF * 32 * 16;
 constexpr uint32_t MAX_RESIDENT_WARPS = 4096;  // warps of the persistent forward launch that own a hit list
 struct StateLayout {
     size_t planes, steps_executed, warp_tail, ray_pix, warp_mask, warp_off, ray_count, work_counter, hitlist, total;
@@ -136,7 +141,7 @@ __host__ __device__ inline StateLayout state_layout(uint32_t w, uint32_t h, uint
     L.ray_count = o, o = align_up(o + (size_t)S * 4, 256);
     L.work_counter = o, o = align_up(o + (size_t)S * 4, 256);
     // per-resident-warp hit lists of the forward ((64 list + 16 batch) entries x 32 lanes x 8 B = 20 KiB each)
-    L.hitlist = o, o = align_up(o + (size_t)min_u32(L.num_warps + 3, MAX_RESIDENT_WARPS) * (LIST_CAP + KBUF) * 32 * 8, 256);
+    L.hitlist = o, o = align_up(o + (size_t)min_u32(L.num_warps + 3, MAX_RESIDENT_WARPS) * HITLIST_WARP_BYTES, 256);
     L.total = o;
     return L;
 }

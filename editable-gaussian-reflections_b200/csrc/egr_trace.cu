@@ -44,26 +44,36 @@ struct StepCfg {
 };
 
 // Per-ray hit list of the collection passes: the (up to) LIST_CAP nearest accepted hits beyond the window, as an
-// unordered set in global memory (slot-major, lanes interleaved; a few tens of MB for the whole machine, L2
-// resident).  16-wide batches are selected from it; a BVH walk is repeated only when a ray has consumed all 64 and
-// is still not opaque.  Appending is one 8-byte store; only rays with more than 64 hits pay for replace-the-farthest.
+// unordered set in global memory (slot-major, lanes interleaved; L2 resident).  16-wide batches are selected from
+// the distances alone; (leaf, alpha) of a selected hit is fetched once, so that compositing does not evaluate the
+// Gaussian a second time.  A BVH walk is repeated only when a ray has consumed all LIST_CAP and is still not opaque;
+// only such rays pay for replace-the-farthest.
 struct LaneList {
-    uint2 *base;      // this warp's region
+    float *t;         // [LIST_CAP][32] this warp's distances
+    uint2 *la;        // [LIST_CAP][32] (leaf, alpha bits)
+    uint4 *batch;     // [KBUF][32] the selected batch (t, leaf, alpha, -)
     uint32_t cnt;     // hits beyond the window seen by the current collection pass (may exceed LIST_CAP)
     float maxt;       // farthest distance held (valid once cnt >= 1)
     uint32_t maxslot;
 };
+__device__ __forceinline__ void list_bind(LaneList &L, char *region) {
+    L.t = (float *)region;
+    L.la = (uint2 *)(region + HITLIST_T_BYTES);
+    L.batch = (uint4 *)(region + HITLIST_T_BYTES + HITLIST_LA_BYTES);
+}
 __device__ __forceinline__ void list_reset(LaneList &L) { L.cnt = 0, L.maxt = -FLT_MAX, L.maxslot = 0; }
-__device__ __forceinline__ void list_add(LaneList &L, const uint32_t lane, const float t, const uint32_t leaf) {
+__device__ __forceinline__ void list_add(LaneList &L, const uint32_t lane, const float t, const uint32_t leaf, const float alpha) {
     if (L.cnt < LIST_CAP) {
-        L.base[L.cnt * 32 + lane] = make_uint2(__float_as_uint(t), leaf);
+        L.t[L.cnt * 32 + lane] = t;
+        L.la[L.cnt * 32 + lane] = make_uint2(leaf, __float_as_uint(alpha));
         if (t > L.maxt) L.maxt = t, L.maxslot = L.cnt;
     } else if (t < L.maxt) {  // full: the newcomer replaces the farthest entry, then the new farthest is found
-        L.base[L.maxslot * 32 + lane] = make_uint2(__float_as_uint(t), leaf);
+        L.t[L.maxslot * 32 + lane] = t;
+        L.la[L.maxslot * 32 + lane] = make_uint2(leaf, __float_as_uint(alpha));
         float m = -FLT_MAX;
         uint32_t ms = 0;
         for (uint32_t e = 0; e < LIST_CAP; ++e) {
-            const float te = __uint_as_float(L.base[e * 32 + lane].x);
+            const float te = L.t[e * 32 + lane];
             if (te > m) m = te, ms = e;
         }
         L.maxt = m, L.maxslot = ms;
@@ -105,7 +115,7 @@ __device__ __forceinline__ void full_test(
             T_full = (float)((double)T_full * (1.0 - (double)h.alpha));  // shaders.cu:69-71
             n_acc++;
         }
-        if (h.t > w) list_add(L, threadIdx.x & 31, h.t, leaf);  // strict, as forward_pass.cu:62
+        if (h.t > w) list_add(L, threadIdx.x & 31, h.t, leaf, h.alpha);  // strict, as forward_pass.cu:62
     }
 }
 // Warp-uniform stackless walk for coherent rays (the primary rays of an 8x4 tile): ONE node index per warp, every
@@ -191,6 +201,9 @@ __shared__ long long s_dbg_tnode[4], s_dbg_tcand[4];
 #endif
 #ifndef EGR_SELBATCH
 #define EGR_SELBATCH 4
+#endif
+#ifndef EGR_LAGATHER
+#define EGR_LAGATHER 4
 #endif
 #ifndef EGR_QBATCH
 #define EGR_QBATCH 4
@@ -350,7 +363,7 @@ __global__ void k_end(TraceCtx c) {  // raytracer.cpp:91-93 without the host syn
 // ---- one ray-step of one warp's 32 rays ------------------------------------------------------------------------
 template <bool LANE_WALK>
 __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, const int grads, const uint32_t warp,
-                                           const uint32_t lane, float4 *s_rec, uint2 *list) {
+                                           const uint32_t lane, float4 *s_rec, char *list) {
     const EgrConfig &cfg = c.p.config;
     const uint32_t W = c.p.image_width, H = c.p.image_height;
 
@@ -427,7 +440,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
     // primary rays of an 8x4 tile are coherent: one warp-uniform walk; bounce rays fan out: per-lane walks
     constexpr bool lane_walk = LANE_WALK;
     LaneList L;
-    L.base = list;
+    list_bind(L, list);
     list_reset(L);
     // A ray with a non-finite origin / direction (the reference's tangent frame, ggx_brdf.h:163, is 0/0 for a normal
     // of exactly -z) is invalid for OptiX and finds nothing there; here it would pass every box test, so it is not
@@ -451,15 +464,12 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
         // EGR_SELBATCH independent list loads in flight per iteration (the list is written with plain stores and read
         // back from L2: one exposed latency per entry otherwise)
         for (uint32_t e = 0; e < mx; e += EGR_SELBATCH) {
-            uint2 q[EGR_SELBATCH];
+            float q[EGR_SELBATCH];
+#pragma unroll
+            for (int i = 0; i < EGR_SELBATCH; ++i) q[i] = e + i < mine ? L.t[(e + i) * 32 + lane] : -FLT_MAX;  // never selected
 #pragma unroll
             for (int i = 0; i < EGR_SELBATCH; ++i)
-                q[i] = e + i < mine ? L.base[(e + i) * 32 + lane] : make_uint2(0xFF800000u, 0u);  // -inf: never selected
-#pragma unroll
-            for (int i = 0; i < EGR_SELBATCH; ++i) {
-                const float t = __uint_as_float(q[i].x);
-                if (t > w && t < kt[KBUF - 1]) kb_insert(kt, kj, t, q[i].y);
-            }
+                if (q[i] > w && q[i] < kt[KBUF - 1]) kb_insert(kt, kj, q[i], e + i);  // kj = list slot
         }
     };
 
@@ -470,9 +480,9 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
         // has more than LIST_CAP hits: collect the next LIST_CAP nearest with one more walk, then select again
         const bool refill = !done && kt[KBUF - 1] == FLT_MAX && L.cnt > LIST_CAP;
         if (__any_sync(0xffffffffu, refill)) {  // rare: the batches of the other lanes wait in the spill slots
-            uint2 *kpark = L.base + LIST_CAP * 32;
+            // (lanes that do not refill keep their list, so their slots stay valid)
 #pragma unroll
-            for (int i = 0; i < KBUF; ++i) kpark[i * 32 + lane] = make_uint2(__float_as_uint(kt[i]), kj[i]);
+            for (int i = 0; i < KBUF; ++i) L.batch[i * 32 + lane] = make_uint4(__float_as_uint(kt[i]), kj[i], 0u, 0u);
             if (refill) list_reset(L);
             int dummy_acc = 0;
             float dummy_T = 1.0f;
@@ -482,7 +492,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
             if (!refill) {
 #pragma unroll
                 for (int i = 0; i < KBUF; ++i) {
-                    const uint2 kq = kpark[i * 32 + lane];
+                    const uint4 kq = L.batch[i * 32 + lane];
                     kt[i] = __uint_as_float(kq.x), kj[i] = kq.y;
                 }
             }
@@ -506,29 +516,31 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
                 nbatches++;
             }
         }
-        // the batch goes through memory so that the composite loop can index it dynamically (small code): 16 extra
-        // slots behind the warp's hit list (L1/L2 resident; shared memory would be carved out of the L1 the walk
-        // depends on)
-        uint2 *kspill = L.base + LIST_CAP * 32;
+        // the batch goes through memory so that the composite loop can index it dynamically (small code); on the
+        // way, (leaf, alpha) of the selected slots are gathered, EGR_LAGATHER independent loads at a time
 #pragma unroll
-        for (int i = 0; i < KBUF; ++i) kspill[i * 32 + lane] = make_uint2(__float_as_uint(kt[i]), kj[i]);
+        for (int h0 = 0; h0 < KBUF; h0 += EGR_LAGATHER) {
+            uint2 la[EGR_LAGATHER];
+#pragma unroll
+            for (int i = 0; i < EGR_LAGATHER; ++i)
+                la[i] = kt[h0 + i] < FLT_MAX ? L.la[kj[h0 + i] * 32 + lane] : make_uint2(0xFFFFFFFFu, 0u);
+#pragma unroll
+            for (int i = 0; i < EGR_LAGATHER; ++i)
+                L.batch[(h0 + i) * 32 + lane] = make_uint4(__float_as_uint(kt[h0 + i]), la[i].x, la[i].y, 0u);
+        }
         for (int i = 0; i < KBUF; ++i) {
             if (!__any_sync(0xffffffffu, !done)) break;
             if (!done) {
-                const uint2 kq = kspill[i * 32 + lane];
+                const uint4 kq = L.batch[i * 32 + lane];
                 const float t = __uint_as_float(kq.x);
                 w = fmaxf(w, t);  // forward_pass.cu:89
                 if (t < sc.tmax) {
                     const uint32_t j = kq.y;
-                    float4 r0, r1, r2, r3;
-                    ldg2(&c.bvh.records[4 * (size_t)j], r0, r1);
-                    ldg2(&c.bvh.records[4 * (size_t)j + 2], r2, r3);
-                    HitEval h;
-                    eval_hit(r0, r1, r2, r3, o, d, sc.tmin, sc.tmax, sc.exp_power, h);  // same bits as in the walk
+                    const float alpha = __uint_as_float(kq.z);  // as evaluated by the walk
                     const float4 a0 = __ldg(&c.bvh.appearance[3 * (size_t)j + 0]);
                     const float4 a1 = __ldg(&c.bvh.appearance[3 * (size_t)j + 1]);
                     const float4 a2 = __ldg(&c.bvh.appearance[3 * (size_t)j + 2]);
-                    const float nextT = T * (1.0f - h.alpha);  // forward_pass.cu:108-115
+                    const float nextT = T * (1.0f - alpha);  // forward_pass.cu:108-115
                     const float wt = T - nextT;
                     c_rgb = fma3(mk3(a0.x, a0.y, a0.z), wt, c_rgb);
                     c_n = fma3(mk3(a1.x, a1.y, a1.z), wt, c_n);
@@ -536,7 +548,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
                     c_rough = fmaf(a0.w, wt, c_rough);
                     c_depth = fmaf(t, wt, c_depth);
                     T = nextT;
-                    if (chunk) chunk[i * 32 + lane] = make_float4(__uint_as_float(j), t, h.alpha, T);
+                    if (chunk) chunk[i * 32 + lane] = make_float4(__uint_as_float(j), t, alpha, T);
                     nh++;
                     if (T < T_thr) {  // forward_pass.cu:131-134
                         w = sc.tmax;
@@ -675,7 +687,7 @@ __global__ void __launch_bounds__(32 * WARPS, 20 / WARPS) k_trace_step(const Tra
     const int B = min(*c.p.config.num_bounces, (int)c.S - 1);  // shaders.cu:85
     if (step > B) return;
     const uint32_t groups = step == 0 ? c.num_warps : (c.ray_count[step] + 31) / 32;
-    uint2 *list = c.hitlist + (size_t)(blockIdx.x * WARPS + wib) * (LIST_CAP + KBUF) * 32;
+    char *list = c.hitlist + (size_t)(blockIdx.x * WARPS + wib) * HITLIST_WARP_BYTES;
     while (true) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(&c.work_counter[step], 1u);
@@ -696,7 +708,7 @@ __global__ void __launch_bounds__(32 * WARPS, 20 / WARPS) k_trace_step(const Tra
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1_));
             uint32_t sm_;
             asm volatile("mov.u32 %0, %%smid;" : "=r"(sm_));
-            uint4 *dbg = (uint4 *)(c.hitlist + (size_t)3000 * (LIST_CAP + KBUF) * 32) + (size_t)step * 32768;
+            uint4 *dbg = (uint4 *)(c.hitlist + (size_t)3000 * HITLIST_WARP_BYTES) + (size_t)step * 32768;
             uint32_t nmax = s_dbg_nodes[threadIdx.x], nsum = nmax, rmax = s_dbg_rounds[threadIdx.x];
             for (int o_ = 16; o_ > 0; o_ >>= 1) {
                 nmax = max(nmax, __shfl_xor_sync(0xffffffffu, nmax, o_));
@@ -799,7 +811,7 @@ static int make_ctx(const EgrParams *p, TraceCtx &c) {
     c.warp_off = (uint32_t *)(sb + L.warp_off);
     c.ray_count = (uint32_t *)(sb + L.ray_count);
     c.work_counter = (uint32_t *)(sb + L.work_counter);
-    c.hitlist = (uint2 *)(sb + L.hitlist);
+    c.hitlist = sb + L.hitlist;
     c.P = L.P, c.S = L.S, c.tiles_x = tiles_x(p->image_width), c.num_warps = L.num_warps;
     {
         const char *e = getenv("EGR_FORCE_WALK");  // debugging aid: 1 = warp-uniform walk everywhere, 2 = per-lane

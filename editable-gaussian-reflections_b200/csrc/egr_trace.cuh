@@ -15,7 +15,7 @@ struct TraceCtx {
     uint32_t *warp_off;        // [S][num_warps]
     uint32_t *ray_count;       // [S]
     uint32_t *work_counter;    // [S] next 32-ray group of the persistent forward launch
-    uint2 *hitlist;            // [resident warps][64][32] (t, leaf) of every hit of the ray being traced
+    char *hitlist;             // [resident warps][HITLIST_WARP_BYTES] hit lists of the rays being traced (egr_common.cuh)
     uint32_t P, S, tiles_x, num_warps;
     uint32_t hitlog_chunks;    // capacity in chunks
     int force_walk;            // 0 = auto (warp-uniform walk for step 0, per-lane for bounces)
