@@ -85,6 +85,7 @@ SYMBOLS = {
     "egr_bvh_refit": (C.c_int, [C.POINTER(EgrGaussians), C.POINTER(EgrConfig), _FP, C.c_size_t, _FP]),
     "egr_pixel_state_bytes": (C.c_size_t, [C.c_uint32, C.c_uint32, C.c_uint32]),
     "egr_hitlog_bytes_for_hits": (C.c_size_t, [C.c_uint64]),
+    "egr_camera_set_pose": (C.c_int, [C.POINTER(EgrCamera), C.POINTER(C.c_float), C.POINTER(C.c_float), _FP]),
     "egr_raytrace": (C.c_int, [C.POINTER(EgrParams), C.c_int, _FP]),
     "egr_raytrace_phases": (C.c_int, [C.POINTER(EgrParams), C.c_int, C.c_uint32, _FP]),
     "egr_reset_accumulators": (C.c_int, [C.POINTER(EgrParams), _FP]),

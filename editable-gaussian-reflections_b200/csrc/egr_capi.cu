@@ -21,3 +21,33 @@ extern "C" int egr_roughness_downweight_grad(void) { return 1; }
 extern "C" double egr_roughness_downweight_grad_power(void) { return (double)egr::ROUGH_DOWNWEIGHT_POW; }
 extern "C" int egr_buffer_size(void) { return egr::KBUF; }
 extern "C" int egr_max_iterations(void) { return egr::MAX_ITERATIONS; }
+
+namespace egr {
+struct PoseArgs {
+    float o[3], r[9];
+    int has_o, has_r;
+};
+__global__ void k_set_pose(EgrCamera cam, PoseArgs a) {
+    const int i = threadIdx.x;
+    if (a.has_o && i < 3) const_cast<float *>(cam.origin)[i] = a.o[i];
+    if (a.has_r && i < 9) {
+        const_cast<float *>(cam.rotation_c2w)[i] = a.r[i];
+        const_cast<float *>(cam.rotation_w2c)[(i % 3) * 3 + i / 3] = a.r[i];  // camera.h:69-76
+    }
+}
+}  // namespace egr
+
+extern "C" int egr_camera_set_pose(const EgrCamera *cam, const float *host_origin, const float *host_rotation_c2w,
+                                   void *stream) {
+    if (!cam || !cam->origin || !cam->rotation_c2w || !cam->rotation_w2c) {
+        egr::set_error("egr_camera_set_pose: camera pointers are null");
+        return EGR_EINVAL;
+    }
+    egr::PoseArgs a = {};
+    a.has_o = host_origin != nullptr, a.has_r = host_rotation_c2w != nullptr;
+    for (int i = 0; i < 3 && a.has_o; ++i) a.o[i] = host_origin[i];
+    for (int i = 0; i < 9 && a.has_r; ++i) a.r[i] = host_rotation_c2w[i];
+    egr::k_set_pose<<<1, 32, 0, (cudaStream_t)stream>>>(*cam, a);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}

@@ -51,9 +51,23 @@ class CameraDataHolder(_Holder):  # camera.h:43-77
         if tuple(c2w_origin.shape) != (3,):
             raise RuntimeError("c2w_origin must be 3")
         with torch.no_grad():
-            self.rotation_c2w.copy_(c2w_rotation)
-            self.origin.copy_(c2w_origin)
-            self.rotation_w2c.copy_(c2w_rotation.transpose(0, 1))
+            # parts that live in host memory travel as kernel arguments of one tiny launch (egr_camera_set_pose):
+            # a `copy_` from a host tensor would block the host until the stream has drained
+            host_o = self.origin.is_cuda and c2w_origin.device.type == "cpu"
+            host_r = self.origin.is_cuda and c2w_rotation.device.type == "cpu"
+            if host_o or host_r:
+                cam = _capi.EgrCamera()
+                for f in _capi.CAMERA_FIELDS:
+                    setattr(cam, f, getattr(self, f).data_ptr())
+                o = (C.c_float * 3)(*c2w_origin.detach().to(torch.float32).reshape(-1).tolist()) if host_o else None
+                r = (C.c_float * 9)(*c2w_rotation.detach().to(torch.float32).reshape(-1).tolist()) if host_r else None
+                _capi.check(_capi.load().egr_camera_set_pose(C.byref(cam), o, r,
+                                                             torch.cuda.current_stream(self.origin.device).cuda_stream))
+            if not host_r:
+                self.rotation_c2w.copy_(c2w_rotation)
+                self.rotation_w2c.copy_(c2w_rotation.transpose(0, 1))
+            if not host_o:
+                self.origin.copy_(c2w_origin)
 
 
 class ConfigDataHolder(_Holder):  # config.h:31-51 (same defaults)

@@ -77,7 +77,9 @@ class GaussianRaytracer:
                  znear=0.01, zfar=999.9):
         with torch.no_grad():
             R = viewpoint_camera.R
-            R = torch.from_numpy(R).cuda().float() if isinstance(R, np.ndarray) else R.cuda()
+            # a numpy pose stays on the host (the reference uploads it with a blocking `.cuda()`); set_pose passes
+            # host parts by value
+            R = torch.from_numpy(np.ascontiguousarray(R, dtype=np.float32)) if isinstance(R, np.ndarray) else R.float()
             R_c2w_blender = -R
             R_c2w_blender[:, 0] = -R_c2w_blender[:, 0]
             camera = self.cuda_module.get_camera()

@@ -191,6 +191,13 @@ int egr_raytrace(const EgrParams *p, int grads_enabled, void *stream);
 #define EGR_PHASE_ALL 0xFFFFFFFFu
 int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32_t phase_mask, void *stream);
 
+/* CameraDataHolder::set_pose (csrc/core/camera.h:43-77) for a pose that lives in HOST memory: origin[3] and the
+ * row-major c2w rotation[9] are read during this call and travel as kernel arguments of one tiny launch that writes
+ * origin, rotation_c2w and rotation_w2c (= transpose).  No staging buffer, no host synchronisation (the reference's
+ * `tensor.copy_` of a pageable host tensor blocks the host until every earlier launch on the stream has finished).
+ * Either pointer may be NULL to leave that part unchanged. */
+int egr_camera_set_pose(const EgrCamera *cam, const float *host_origin, const float *host_rotation_c2w, void *stream);
+
 /* FramebufferDataHolder::reset_accumulators (csrc/core/framebuffer.h:249-258) as one launch. */
 int egr_reset_accumulators(const EgrParams *p, void *stream);
 /* DenoiserWrapper::run (csrc/optix/denoiser_wrapper.h:76-104): the OptiX AI denoiser is a proprietary

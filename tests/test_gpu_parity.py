@@ -365,6 +365,32 @@ def test_renderer_facade_host_targets_overlapped_upload(small):
             assert scale > 0 and float((a - b).abs().max()) <= 1e-4 * scale
 
 
+def test_set_pose_from_host_memory_matches_device_copy(small):
+    """A pose held in host tensors goes through egr_camera_set_pose (kernel arguments, no host sync); same bits as
+    the device-side copy_ path, including the transposed w2c matrix and partial (mixed host/device) updates."""
+    import torch
+
+    sc, cam, W, Hh = small
+    rt = H.make_gpu_raytracer(sc, cam, dict(num_bounces=0))
+    c = rt.get_camera()
+    g = np.random.default_rng(3)
+    o = torch.from_numpy(g.normal(size=3).astype(np.float32))
+    r = torch.from_numpy(g.normal(size=(3, 3)).astype(np.float32))
+    c.set_pose(o.cuda(), r.cuda())
+    ref = [t.clone() for t in (c.origin, c.rotation_c2w, c.rotation_w2c)]
+    for t in (c.origin, c.rotation_c2w, c.rotation_w2c):
+        t.zero_()
+    c.set_pose(o, r)  # both on the host
+    for a, b in zip(ref, (c.origin, c.rotation_c2w, c.rotation_w2c)):
+        assert torch.equal(a, b)
+    assert torch.equal(c.rotation_w2c, c.rotation_c2w.t())
+    c.origin.zero_()
+    c.set_pose(o, r.cuda())  # mixed
+    assert torch.equal(c.origin, ref[0]) and torch.equal(c.rotation_c2w, ref[1])
+    with pytest.raises(RuntimeError):
+        c.set_pose(o, r[:2])
+
+
 def test_overlapped_backward_equals_serial_backward(small):
     """One raytrace() call runs the backward of step s-1 on a side stream under the forward of step s; the same
     launches issued one call at a time run serially.  Same gradients (float atomics: order-level differences)."""
