@@ -34,6 +34,8 @@ STATS_FIELDS = ["num_accumulated_per_pixel", "num_traversed_per_pixel", "num_hit
                 "num_composited_per_pixel", "num_steps_per_pixel", "hitlog_status"]
 
 EgrCamera = _ptr_struct("EgrCamera", CAMERA_FIELDS)
+GRAD_TARGET_FIELDS = ["mean", "opacity", "scale", "roughness", "rotation", "rgb", "normal", "f0"]
+EgrGradTargets = _ptr_struct("EgrGradTargets", GRAD_TARGET_FIELDS)
 EgrConfig = _ptr_struct("EgrConfig", CONFIG_FIELDS)
 EgrFramebuffer = _ptr_struct("EgrFramebuffer", FRAMEBUFFER_FIELDS)
 EgrMetadata = _ptr_struct("EgrMetadata", METADATA_FIELDS)
@@ -86,6 +88,7 @@ SYMBOLS = {
     "egr_pixel_state_bytes": (C.c_size_t, [C.c_uint32, C.c_uint32, C.c_uint32]),
     "egr_hitlog_bytes_for_hits": (C.c_size_t, [C.c_uint64]),
     "egr_camera_set_pose": (C.c_int, [C.POINTER(EgrCamera), C.POINTER(C.c_float), C.POINTER(C.c_float), _FP]),
+    "egr_gradients_accumulate": (C.c_int, [_FP, C.c_uint32, C.POINTER(EgrGradTargets), _FP]),
     "egr_raytrace": (C.c_int, [C.POINTER(EgrParams), C.c_int, _FP]),
     "egr_raytrace_phases": (C.c_int, [C.POINTER(EgrParams), C.c_int, C.c_uint32, _FP]),
     "egr_reset_accumulators": (C.c_int, [C.POINTER(EgrParams), _FP]),

@@ -51,3 +51,48 @@ extern "C" int egr_camera_set_pose(const EgrCamera *cam, const float *host_origi
     EGR_CUDA_TRY(cudaGetLastError());
     return EGR_OK;
 }
+
+namespace egr {
+// one thread per (Gaussian, float4 column group of the record): coalesced 16-byte reads of the record
+__global__ void __launch_bounds__(256) k_grad_accumulate(const float4 *__restrict__ rec, uint32_t n, EgrGradTargets d) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)n * (EGR_GRAD_STRIDE / 4)) return;
+    const uint32_t g = (uint32_t)(i / (EGR_GRAD_STRIDE / 4)), q = (uint32_t)(i % (EGR_GRAD_STRIDE / 4));
+    const float4 v = rec[i];
+    auto add3 = [](float *p, size_t k, float x, float y, float z) {
+        if (p) p[3 * k] += x, p[3 * k + 1] += y, p[3 * k + 2] += z;
+    };
+    switch (q) {  // column map: include/egr_b200.h, EgrGaussians
+    case 0: add3(d.mean, g, v.x, v.y, v.z); if (d.opacity) d.opacity[g] += v.w; break;
+    case 1: add3(d.scale, g, v.x, v.y, v.z); if (d.roughness) d.roughness[g] += v.w; break;
+    case 2:
+        if (d.rotation) {
+            float4 *r = reinterpret_cast<float4 *>(d.rotation) + g;
+            float4 o = *r;
+            o.x += v.x, o.y += v.y, o.z += v.z, o.w += v.w;
+            *r = o;
+        }
+        break;
+    case 3: add3(d.rgb, g, v.x, v.y, v.z); break;
+    case 4: add3(d.normal, g, v.x, v.y, v.z); break;
+    default: add3(d.f0, g, v.x, v.y, v.z); break;
+    }
+}
+}  // namespace egr
+
+extern "C" int egr_gradients_accumulate(const float *grad_records, uint32_t count, const EgrGradTargets *dst, void *stream) {
+    if (!grad_records || !dst) {
+        egr::set_error("egr_gradients_accumulate: null argument");
+        return EGR_EINVAL;
+    }
+    if (dst->rotation && ((uintptr_t)dst->rotation & 15u)) {
+        egr::set_error("egr_gradients_accumulate: the rotation target must be 16-byte aligned");
+        return EGR_EINVAL;
+    }
+    if (count == 0) return EGR_OK;
+    const size_t threads = (size_t)count * (EGR_GRAD_STRIDE / 4);
+    egr::k_grad_accumulate<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const float4 *>(grad_records), count, *dst);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}

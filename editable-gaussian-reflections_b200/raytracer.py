@@ -391,6 +391,16 @@ class Raytracer:
         self._build_params()
 
     # ---- test / debug helpers (not in the reference) ---------------------------------------------------------
+    def accumulate_gradients_into(self, targets: dict):
+        """targets[name] += gradient of `name` for the eight parameters, one launch (egr_gradients_accumulate).
+        Not in the reference class: its caller does this with eight `add_` (gaussian_raytracer.py:53-62)."""
+        t = _capi.EgrGradTargets()
+        for f in _capi.GRAD_TARGET_FIELDS:
+            setattr(t, f, targets[f].data_ptr() if targets.get(f) is not None else None)
+        g = self.gaussian_data
+        _capi.check(self._lib.egr_gradients_accumulate(g.grad_records.data_ptr(), int(g.grad_records.shape[0]),
+                                                       C.byref(t), self._stream()))
+
     def export_bvh(self):
         """Copies of (sorted_ids [n], records [n,16], nodes [2n-1,8], parents [2n-1])."""
         n = self.gaussian_data.count

@@ -198,6 +198,15 @@ int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32_t phase_ma
  * Either pointer may be NULL to leave that part unchanged. */
 int egr_camera_set_pose(const EgrCamera *cam, const float *host_origin, const float *host_rotation_c2w, void *stream);
 
+/* GaussianRaytracer._import_param_gradients (editable_gauss_refl/renderer/gaussian_raytracer.py:53-62: eight
+ * `param.grad.add_(holder.grad)`) as ONE launch: dst[k] += column group k of the flat gradient record, each dst a
+ * contiguous [N, ch] fp32 array of the caller (the model's .grad tensors); a NULL dst is skipped.  Reads the record
+ * once (96 B/Gaussian) instead of eight strided passes over it. */
+typedef struct EgrGradTargets {
+    float *mean, *opacity, *scale, *roughness, *rotation, *rgb, *normal, *f0; /* [N,3] [N,1] [N,3] [N,1] [N,4] [N,3] [N,3] [N,3] */
+} EgrGradTargets;
+int egr_gradients_accumulate(const float *grad_records, uint32_t count, const EgrGradTargets *dst, void *stream);
+
 /* FramebufferDataHolder::reset_accumulators (csrc/core/framebuffer.h:249-258) as one launch. */
 int egr_reset_accumulators(const EgrParams *p, void *stream);
 /* DenoiserWrapper::run (csrc/optix/denoiser_wrapper.h:76-104): the OptiX AI denoiser is a proprietary

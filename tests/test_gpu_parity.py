@@ -365,6 +365,31 @@ def test_renderer_facade_host_targets_overlapped_upload(small):
             assert scale > 0 and float((a - b).abs().max()) <= 1e-4 * scale
 
 
+def test_fused_gradient_import_equals_eight_adds(small):
+    """egr_gradients_accumulate (one launch over the flat record) against the reference's eight add_ calls:
+    identical sums, NULL targets skipped, accumulation on top of existing values."""
+    import torch
+
+    sc, cam, W, Hh = small
+    rt = H.make_gpu_raytracer(sc, cam, dict(num_bounces=1, loss_weight_diffuse=5.0))
+    H.set_targets(rt, scenes.random_targets(W, Hh, seed=7))
+    with torch.enable_grad():
+        rt.raytrace()
+    g = rt.get_gaussians()
+    names = ("mean", "opacity", "scale", "roughness", "rotation", "rgb", "normal", "f0")
+    gen = torch.Generator(device="cuda").manual_seed(1)
+    base = {k: torch.randn(getattr(g, k).shape, device="cuda", generator=gen) for k in names}
+    want = {k: base[k] + getattr(g, k).grad for k in names}
+    got = {k: base[k].clone() for k in names}
+    rt.accumulate_gradients_into(got)
+    for k in names:
+        assert torch.equal(got[k], want[k]), k
+    assert float(want["mean"].sub(base["mean"]).abs().max()) > 0
+    part = {k: base[k].clone() for k in ("rgb", "rotation")}
+    rt.accumulate_gradients_into(part)  # the other six targets are NULL
+    assert torch.equal(part["rgb"], want["rgb"]) and torch.equal(part["rotation"], want["rotation"])
+
+
 def test_set_pose_from_host_memory_matches_device_copy(small):
     """A pose held in host tensors goes through egr_camera_set_pose (kernel arguments, no host sync); same bits as
     the device-side copy_ path, including the transposed w2c matrix and partial (mixed host/device) updates."""
