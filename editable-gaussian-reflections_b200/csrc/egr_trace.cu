@@ -202,6 +202,9 @@ __shared__ long long s_dbg_tnode[4], s_dbg_tcand[4];
 #ifndef EGR_SELBATCH
 #define EGR_SELBATCH 4
 #endif
+#ifndef EGR_LANE_WARPS
+#define EGR_LANE_WARPS 28
+#endif
 #ifndef EGR_LAGATHER
 #define EGR_LAGATHER 4
 #endif
@@ -678,10 +681,12 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
 // Persistent launch: as many blocks as fit on the machine, every warp fetches the next 32-ray group (an 8x4 tile at
 // step 0, 32 compacted rays at a bounce step) from a counter until the step is done; a resident warp owns one hit-list
 // region for its whole life, so the lists of a step occupy a few tens of MB and stay in L2.
+// The bounce launch is compiled for 28 warps per SM (72 registers, a few spilled values): with many bounce rays the
+// extra warps hide more latency (C3: 31.3 -> 28.2 ms per frame); the primary launch keeps 20 warps of 96 registers.
 // The bounce launch uses one-warp blocks: a block's registers are released as soon as its own warp runs out of work,
 // which lets the blocks of the overlapped backward in while the long tasks of the bounce step drain.
 template <bool LANE_WALK, int WARPS>
-__global__ void __launch_bounds__(32 * WARPS, 20 / WARPS) k_trace_step(const TraceCtx c, const int step, const int grads) {
+__global__ void __launch_bounds__(32 * WARPS, (LANE_WALK ? EGR_LANE_WARPS : 20) / WARPS) k_trace_step(const TraceCtx c, const int step, const int grads) {
     __shared__ float4 s_rec[LANE_WALK ? 1 : WARPS][LANE_WALK ? 1 : FAT * 4];
     const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int B = min(*c.p.config.num_bounces, (int)c.S - 1);  // shaders.cu:85
@@ -824,6 +829,7 @@ static int make_ctx(const EgrParams *p, TraceCtx &c) {
 int launch_backward_impl(const TraceCtx &c, uint32_t step_mask, cudaStream_t st);
 
 // Blocks of k_trace_step the current device keeps resident (occupancy x SM count), capped by the hit-list scratch.
+static uint32_t g_lane_blocks[64] = {0};  // one-warp blocks of the bounce launch per device
 static uint32_t resident_blocks() {
     static uint32_t cached[64] = {0};  // per device; the queries take driver locks, keep them off the per-call path
     int dev = 0;
@@ -834,7 +840,8 @@ static uint32_t resident_blocks() {
     int per_sm_lane = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_step<false, 4>, 128, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_lane, k_trace_step<true, 1>, 32, 0);
-    per_sm = min(per_sm, per_sm_lane / 4);  // both launches use the same number of resident warps (hit-list regions)
+    (void)per_sm_lane;
+    g_lane_blocks[dev] = (uint32_t)min(sms * per_sm_lane, (int)MAX_RESIDENT_WARPS);
     const uint32_t nb = (uint32_t)max(1, sms * per_sm);
     cached[dev] = min(nb, (uint32_t)(MAX_RESIDENT_WARPS / 4));
     return cached[dev];
@@ -922,7 +929,10 @@ extern "C" int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32
             if (s > 0) k_scan_spawned<<<1, 1024, 0, st>>>(c, (int)s);
             // primary rays of an 8x4 tile are coherent: warp-uniform walk; bounce rays fan out: per-lane walks
             const bool lane_walk = c.force_walk == 2 || (c.force_walk == 0 && s > 0);
-            if (lane_walk) k_trace_step<true, 1><<<blocks * 4, 32, 0, st>>>(c, (int)s, grads_enabled);
+            int dev_ = 0;
+            cudaGetDevice(&dev_);
+            const uint32_t lane_blocks = min(g_lane_blocks[dev_ & 63], (c.num_warps + 3) / 4 * 4);  // <= hit-list regions
+            if (lane_walk) k_trace_step<true, 1><<<lane_blocks, 32, 0, st>>>(c, (int)s, grads_enabled);
             else k_trace_step<false, 4><<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
         }
     if (phase_mask & EGR_PHASE_FINISH) {
