@@ -713,7 +713,8 @@ __global__ void __launch_bounds__(32 * WARPS, (LANE_WALK ? EGR_LANE_WARPS : 20) 
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1_));
             uint32_t sm_;
             asm volatile("mov.u32 %0, %%smid;" : "=r"(sm_));
-            uint4 *dbg = (uint4 *)(c.hitlist + (size_t)3000 * HITLIST_WARP_BYTES) + (size_t)step * 32768;
+            // the stamps go into the last 4 MiB of the hit log (grad mode with a log far larger than the step needs)
+            uint4 *dbg = (uint4 *)((char *)c.p.hitlog + ((size_t)c.hitlog_chunks - 512) * HITLOG_CHUNK_BYTES) + (size_t)step * 32768;
             uint32_t nmax = s_dbg_nodes[threadIdx.x], nsum = nmax, rmax = s_dbg_rounds[threadIdx.x];
             for (int o_ = 16; o_ > 0; o_ >>= 1) {
                 nmax = max(nmax, __shfl_xor_sync(0xffffffffu, nmax, o_));
@@ -721,7 +722,7 @@ __global__ void __launch_bounds__(32 * WARPS, (LANE_WALK ? EGR_LANE_WARPS : 20) 
                 rmax = max(rmax, __shfl_xor_sync(0xffffffffu, rmax, o_));
             }
             const long long tot_ = clock64() - tc0_;
-            if (lane == 0 && g < 32768 && c.num_warps >= 4096) {
+            if (lane == 0 && g < 32768 && grads && c.hitlog_chunks >= 100000) {
                 dbg[g] = make_uint4((uint32_t)t0_, (uint32_t)(t1_ - t0_), nmax | (rmax << 16), nsum);
                 dbg[g + 65536] = make_uint4((uint32_t)(s_dbg_tnode[wib] >> 4), (uint32_t)(s_dbg_tcand[wib] >> 4), (uint32_t)(tot_ >> 4), 0);
             }

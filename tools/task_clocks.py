@@ -1,6 +1,9 @@
+"""Per-task (32-ray group) durations, node visits and the walk / candidate / rest cycle split of the forward launches.
+Needs the library built with EGR_NVCC_EXTRA=-DEGR_TASK_CLOCKS (the kernels then write %globaltimer stamps and
+counters into the unused tail of the hit-list scratch).  Usage: python tools/task_clocks.py"""
 import os, sys
 import numpy as np, torch
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import egr_b200
 from egr_b200 import scenes
 N, R = 1_000_000, 800
@@ -33,9 +36,10 @@ for vi in (17,):
     for k in res[0]:
         pct("step0 " + k, res[0][k]); pct("step1 " + k, res[1][k] - res[0][k])
     ps = rt._pixel_state
-    CAPK = int(os.environ.get('LISTCAP', '64')) + 16
-    hl_bytes = 4096 * CAPK * 32 * 8
-    off = ps.numel() - ((hl_bytes + 255) // 256 * 256) + 3000 * CAPK * 32 * 8
+    hl = rt._hitlog  # the stamps live in the last 512 chunks of the hit log (egr_trace.cu, EGR_TASK_CLOCKS)
+    CH = 8320
+    off = (hl.numel() // CH - 512) * CH
+    ps = hl
     dbg2 = ps[off + 65536 * 16: off + 65536 * 16 + 2 * 32768 * 16].view(torch.int32).cpu().numpy().astype(np.int64).reshape(2, 32768, 4) & 0xFFFFFFFF
     dbg = ps[off: off + 2 * 32768 * 16].view(torch.int32).cpu().numpy().astype(np.int64).reshape(2, 32768, 4) & 0xFFFFFFFF
     for s, ng in ((0, 20000), (1, None)):
