@@ -140,6 +140,20 @@ def kitchen_scene(n=1_000_000, seed=0):
                 roughness=roughness, spacing=h)
 
 
+def catacaustics_scene(n=3_000_000, seed=0):
+    """C4: the kitchen geometry with real-scene-shaped Gaussians: mixed anisotropy (per-axis log-scale spread,
+    random orientation), opacities spread over the logit range, varied roughness / f0."""
+    sc = kitchen_scene(n, seed=seed)
+    g = np.random.default_rng(seed + 17)
+    sc["scale"] = (sc["scale"] + g.normal(0.0, 0.6, (n, 3))).clip(-9.0, math.log(5.0)).astype(np.float32)  # clamp_max 5
+    q = g.normal(size=(n, 4))
+    sc["rotation"] = (q / np.linalg.norm(q, axis=1, keepdims=True)).astype(np.float32)
+    sc["opacity"] = g.uniform(-3.0, 4.0, (n, 1)).astype(np.float32)
+    sc["roughness"] = g.uniform(0.02, 0.6, (n, 1)).astype(np.float32)
+    sc["f0"] = g.uniform(0.02, 0.5, (n, 3)).astype(np.float32)
+    return sc
+
+
 def kitchen_cameras(num=100, width=800, height=800, fovy=0.6911):
     """Inward-looking orbit inside the room (radius 1.6 m, height 1.5 m, looking slightly down at the centre)."""
     cams = []

@@ -3,9 +3,12 @@
 
   C1  50k random Gaussians, 256x256, 1 bounce, fwd+bwd, checked against the CPU oracle at full size
   C3  kitchen scene, 1920x1080, 3 reflection bounces (max_bounces=3), forward only, 16 accumulated calls
+  C4  3M anisotropic Gaussians, 1024x768 views sharded over the ranks of a torchrun job (one view per rank per step),
+      train iteration with one gradient all-reduce; run as
+      python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 tools/run_configs.py c4
   C5  10M Gaussians: bounding-box selection move / delete / duplicate, refit / rebuild + 1080p 3-bounce re-render
 
-Prints one JSON line per config.  Usage: python tools/run_configs.py [c1] [c3] [c5] [--n5 N]
+Prints one JSON line per config.  Usage: python tools/run_configs.py [c1] [c3] [c4] [c5] [--n5 N]
 """
 import json
 import os
@@ -194,12 +197,71 @@ def c5(n5):
     print(json.dumps(res))
 
 
+def c4(n4=3_000_000, steps=10, warmup=3):
+    import torch.distributed as dist
+
+    from egr_b200 import distributed
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    W, Hh = 1024, 768
+    sc = scenes.catacaustics_scene(n4, seed=0)
+    pc = scenes.SyntheticModel(sc, device=dev, cfg=dict(loss_weight_depth=0.0, loss_weight_specular=0.01))
+    cams = scenes.kitchen_cameras(64, W, Hh)
+    tg = scenes.random_targets(W, Hh, seed=3)
+    views = [scenes.SyntheticCamera(c, tg, device=dev) for c in cams[:16]]
+    rtr = egr_b200.GaussianRaytracer(pc, W, Hh, ppll_forward_size=1000, ppll_backward_size=120_000_000)
+    rt = rtr.cuda_module
+    rt.get_config().num_bounces.fill_(1)
+    g = rt.get_gaussians()
+    rays = torch.zeros((), dtype=torch.int64, device=dev)
+
+    def step(i):
+        v = views[distributed.shard_views(len(views), rank, world, i)]
+        with torch.enable_grad():
+            egr_b200.render(v, rtr)
+        distributed.allreduce_gradients(g.grad_records)
+        rays.add_(rt.get_stats().num_steps_per_pixel.sum())
+
+    for i in range(warmup):
+        step(i)
+    rays.zero_()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    a = ev()
+    for i in range(steps):
+        step(warmup + i)
+    b = ev()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = distributed.max_over_ranks(a.elapsed_time(b), dev)
+    if world > 1:
+        dist.all_reduce(rays)
+    st = rt.get_stats()
+    res = {"config": f"C4 catacaustics-{n4 // 1_000_000}M 1024x768 1 bounce train iteration, {world} rank(s)",
+           "n_gpus": world, "ms_per_step": ms / steps, "views_per_s": world * steps / (ms * 1e-3),
+           "mrays_s": int(rays.item()) / (ms * 1e-3) / 1e6, "hitlog_overflow": int(st.hitlog_status[2].item()),
+           "hits_per_primary_ray": float(st.num_hits_per_pixel.sum().item()) / (W * Hh),
+           "pass": bool(torch.isfinite(g.grad_records).all()) and int(st.hitlog_status[2].item()) == 0}
+    if rank == 0:
+        print(json.dumps(res))
+    if world > 1:
+        dist.destroy_process_group()
+
+
 if __name__ == "__main__":
     args = [a.lower() for a in sys.argv[1:]]
     n5 = 10_000_000
     if "--n5" in args:
         n5 = int(args[args.index("--n5") + 1])
-    which = [a for a in args if a in ("c1", "c3", "c5")] or ["c1", "c3", "c5"]
-    torch.cuda.set_device(0)
+    which = [a for a in args if a in ("c1", "c3", "c4", "c5")] or ["c1", "c3", "c5"]
+    if "c4" not in which:
+        torch.cuda.set_device(0)
     for w in which:
-        {"c1": c1, "c3": c3, "c5": lambda: c5(n5)}[w]()
+        {"c1": c1, "c3": c3, "c4": c4, "c5": lambda: c5(n5)}[w]()
