@@ -209,7 +209,7 @@ __shared__ long long s_dbg_tnode[4], s_dbg_tcand[4];
 #define EGR_LAGATHER 4
 #endif
 #ifndef EGR_QBATCH
-#define EGR_QBATCH 4
+#define EGR_QBATCH 8
 #endif
 constexpr uint32_t FAT_LANE = EGR_FAT_LANE;  // <= 32: the survivors of one range are a 32-bit mask
 template <bool PASS0>
