@@ -89,6 +89,8 @@ SYMBOLS = {
     "egr_hitlog_bytes_for_hits": (C.c_size_t, [C.c_uint64]),
     "egr_camera_set_pose": (C.c_int, [C.POINTER(EgrCamera), C.POINTER(C.c_float), C.POINTER(C.c_float), _FP]),
     "egr_gradients_accumulate": (C.c_int, [_FP, C.c_uint32, C.POINTER(EgrGradTargets), _FP]),
+    "egr_knn3_scratch_bytes": (C.c_size_t, [C.c_uint32]),
+    "egr_knn3_mean_dist2": (C.c_int, [_FP, C.c_uint32, _FP, _FP, C.c_size_t, _FP]),
     "egr_raytrace": (C.c_int, [C.POINTER(EgrParams), C.c_int, _FP]),
     "egr_raytrace_phases": (C.c_int, [C.POINTER(EgrParams), C.c_int, C.c_uint32, _FP]),
     "egr_reset_accumulators": (C.c_int, [C.POINTER(EgrParams), _FP]),

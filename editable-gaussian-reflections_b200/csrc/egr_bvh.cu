@@ -4,6 +4,8 @@
 // (editable_gauss_refl/cuda/csrc/optix/bvh_wrapper.h:24-157, bvh_wrapper.cu:9-70).
 #include <cub/device/device_radix_sort.cuh>
 
+#include <float.h>
+
 #include <mutex>
 
 #include "egr_common.cuh"
@@ -188,6 +190,41 @@ k_preorder(int n, const uint32_t *__restrict__ child_l, const uint32_t *__restri
     if (is_leaf) leaf_node[idx] = pre;
 }
 
+// Bottom-up box propagation from a finished leaf: the second arrival at a node merges its children and continues
+// upward; the arrival counters re-arm themselves for the next pass.
+__device__ __forceinline__ void merge_boxes_upward(const BvhView &bvh, uint32_t node) {
+    uint32_t p = bvh.parents[node];
+    while (p != NO_PARENT) {
+        __threadfence();
+        uint32_t old = atomicAdd(&bvh.flags[p], 1u);
+        if (old == 0) return;  // first arrival: the sibling subtree is not finished yet
+        bvh.flags[p] = 0;      // second (last) arrival re-arms the counter for the next refit
+        uint32_t lc = p + 1;
+        float4 la = __ldcg(&bvh.nodes[2 * (size_t)lc]), lb = __ldcg(&bvh.nodes[2 * (size_t)lc + 1]);
+        uint32_t rc = __float_as_uint(la.w);  // right child = skip of the left child
+        float4 ra = __ldcg(&bvh.nodes[2 * (size_t)rc]), rb = __ldcg(&bvh.nodes[2 * (size_t)rc + 1]);
+        bool le = la.x > lb.x, re = ra.x > rb.x;  // empty boxes (invisible subtrees)
+        float4 a, b;
+        if (le && re) {
+            a = make_float4(1.0f, 1.0f, 1.0f, 0.0f), b = make_float4(-1.0f, -1.0f, -1.0f, 0.0f);
+        } else if (le) {
+            a = ra, b = rb;
+        } else if (re) {
+            a = la, b = lb;
+        } else {
+            a = make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), 0.0f);
+            b = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), 0.0f);
+        }
+        float4 pa = __ldcg(&bvh.nodes[2 * (size_t)p]);
+        float4 pb = __ldcg(&bvh.nodes[2 * (size_t)p + 1]);
+        a.w = pa.w;  // keep skip
+        b.w = pb.w;  // keep the first-leaf tag
+        __stcg(&bvh.nodes[2 * (size_t)p], a);
+        __stcg(&bvh.nodes[2 * (size_t)p + 1], b);
+        p = bvh.parents[p];
+    }
+}
+
 // Geometry record + leaf box for leaf j, then bottom-up box propagation (second arrival continues upward).
 // Reference for the per-Gaussian math: bvh_wrapper.cu:9-59 (_populateBVH), utils/kernel.cu:3-6,
 // utils/activations.cu:5,59,67-69.  The reference's three host syncs (bvh_wrapper.h:38-40) are gone: the config
@@ -248,36 +285,7 @@ __global__ void __launch_bounds__(256) k_refit(BvhView bvh, EgrGaussians g, EgrC
     bvh.nodes[2 * (size_t)node] = make_float4(bmin[0], bmin[1], bmin[2], __uint_as_float(skip));
     bvh.nodes[2 * (size_t)node + 1] = make_float4(bmax[0], bmax[1], bmax[2], __uint_as_float(j));
 
-    uint32_t p = bvh.parents[node];
-    while (p != NO_PARENT) {
-        __threadfence();
-        uint32_t old = atomicAdd(&bvh.flags[p], 1u);
-        if (old == 0) return;  // first arrival: the sibling subtree is not finished yet
-        bvh.flags[p] = 0;      // second (last) arrival re-arms the counter for the next refit
-        uint32_t lc = p + 1;
-        float4 la = __ldcg(&bvh.nodes[2 * (size_t)lc]), lb = __ldcg(&bvh.nodes[2 * (size_t)lc + 1]);
-        uint32_t rc = __float_as_uint(la.w);  // right child = skip of the left child
-        float4 ra = __ldcg(&bvh.nodes[2 * (size_t)rc]), rb = __ldcg(&bvh.nodes[2 * (size_t)rc + 1]);
-        bool le = la.x > lb.x, re = ra.x > rb.x;  // empty boxes (invisible subtrees)
-        float4 a, b;
-        if (le && re) {
-            a = make_float4(1.0f, 1.0f, 1.0f, 0.0f), b = make_float4(-1.0f, -1.0f, -1.0f, 0.0f);
-        } else if (le) {
-            a = ra, b = rb;
-        } else if (re) {
-            a = la, b = lb;
-        } else {
-            a = make_float4(fminf(la.x, ra.x), fminf(la.y, ra.y), fminf(la.z, ra.z), 0.0f);
-            b = make_float4(fmaxf(lb.x, rb.x), fmaxf(lb.y, rb.y), fmaxf(lb.z, rb.z), 0.0f);
-        }
-        float4 pa = __ldcg(&bvh.nodes[2 * (size_t)p]);
-        float4 pb = __ldcg(&bvh.nodes[2 * (size_t)p + 1]);
-        a.w = pa.w;  // keep skip
-        b.w = pb.w;  // keep the first-leaf tag
-        __stcg(&bvh.nodes[2 * (size_t)p], a);
-        __stcg(&bvh.nodes[2 * (size_t)p + 1], b);
-        p = bvh.parents[p];
-    }
+    merge_boxes_upward(bvh, node);
 }
 
 // Activated appearance, permuted to leaf order; runs at the start of every raytrace() so that colour / BRDF edits
@@ -347,6 +355,28 @@ extern "C" int egr_bvh_refit(const EgrGaussians *g, const EgrConfig *cfg, void *
     return EGR_OK;
 }
 
+// Morton order + Karras topology + preorder layout of `n` points (boxes are filled by a refit-like pass afterwards).
+static int build_topology(const float *points, uint32_t n, const BvhView &v, const BuildScratch &B, char *sb, cudaStream_t st) {
+    uint64_t *keys_in = (uint64_t *)(sb + B.keys_in), *keys_out = (uint64_t *)(sb + B.keys_out);
+    uint32_t *ids_in = (uint32_t *)(sb + B.ids_in);
+    uint32_t *child_l = (uint32_t *)(sb + B.child_l), *child_r = (uint32_t *)(sb + B.child_r);
+    uint32_t *parent_int = (uint32_t *)(sb + B.parent_int), *parent_leaf = (uint32_t *)(sb + B.parent_leaf);
+    uint32_t *first = (uint32_t *)(sb + B.first), *last = (uint32_t *)(sb + B.last);
+    k_bounds_init<<<1, 32, 0, st>>>(v.bounds);
+    int nb = (int)min((n + 255u) / 256u, 148u * 8u);
+    k_bounds<<<nb, 256, 0, st>>>(points, n, v.bounds);
+    k_morton<<<(n + 255) / 256, 256, 0, st>>>(points, n, v.bounds, keys_in, ids_in);
+    size_t cub_bytes = B.cub_bytes;
+    EGR_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sb + B.cub_temp, cub_bytes, keys_in, keys_out, ids_in, v.sorted_ids,
+                                                 (int)n, 0, 64, st));
+    if (n > 1) k_karras<<<(n - 1 + 255) / 256, 256, 0, st>>>(keys_out, (int)n, child_l, child_r, parent_int,
+                                                            parent_leaf, first, last);
+    k_preorder<<<(2 * n - 1 + 255) / 256, 256, 0, st>>>((int)n, child_l, parent_int, parent_leaf, first, last, v.nodes,
+                                                        v.parents, v.leaf_node, v.flags);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}
+
 extern "C" int egr_bvh_build(const EgrGaussians *g, const EgrConfig *cfg, void *storage, size_t storage_bytes,
                              void *scratch, size_t scratch_bytes, void *stream) {
     int rc = check_gaussians(g);
@@ -369,25 +399,8 @@ extern "C" int egr_bvh_build(const EgrGaussians *g, const EgrConfig *cfg, void *
     }
     cudaStream_t st = (cudaStream_t)stream;
     BvhView v = bvh_view(storage, n);
-    char *sb = (char *)scratch;
-    uint64_t *keys_in = (uint64_t *)(sb + B.keys_in), *keys_out = (uint64_t *)(sb + B.keys_out);
-    uint32_t *ids_in = (uint32_t *)(sb + B.ids_in);
-    uint32_t *child_l = (uint32_t *)(sb + B.child_l), *child_r = (uint32_t *)(sb + B.child_r);
-    uint32_t *parent_int = (uint32_t *)(sb + B.parent_int), *parent_leaf = (uint32_t *)(sb + B.parent_leaf);
-    uint32_t *first = (uint32_t *)(sb + B.first), *last = (uint32_t *)(sb + B.last);
-
-    k_bounds_init<<<1, 32, 0, st>>>(v.bounds);
-    int nb = (int)min((n + 255u) / 256u, 148u * 8u);
-    k_bounds<<<nb, 256, 0, st>>>(g->mean, n, v.bounds);
-    k_morton<<<(n + 255) / 256, 256, 0, st>>>(g->mean, n, v.bounds, keys_in, ids_in);
-    size_t cub_bytes = B.cub_bytes;
-    EGR_CUDA_TRY(cub::DeviceRadixSort::SortPairs(sb + B.cub_temp, cub_bytes, keys_in, keys_out, ids_in, v.sorted_ids,
-                                                 (int)n, 0, 64, st));
-    if (n > 1) k_karras<<<(n - 1 + 255) / 256, 256, 0, st>>>(keys_out, (int)n, child_l, child_r, parent_int,
-                                                            parent_leaf, first, last);
-    k_preorder<<<(2 * n - 1 + 255) / 256, 256, 0, st>>>((int)n, child_l, parent_int, parent_leaf, first, last, v.nodes,
-                                                        v.parents, v.leaf_node, v.flags);
-    EGR_CUDA_TRY(cudaGetLastError());
+    rc = build_topology(g->mean, n, v, B, (char *)scratch, st);
+    if (rc) return rc;
     return egr_bvh_refit(g, cfg, storage, storage_bytes, stream);
 }
 
@@ -407,6 +420,122 @@ extern "C" int egr_bvh_export(const void *storage, size_t storage_bytes, uint32_
     if (parents) EGR_CUDA_TRY(cudaMemcpyAsync(parents, v.parents, (size_t)L.num_nodes * 4, cudaMemcpyDeviceToDevice, st));
     return EGR_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Mean squared distance to the three nearest neighbours: replaces `distCUDA2` of the reference's
+// simple-knn submodule (submodules/simple-knn/simple_knn.cu:46-222; call sites scene/gaussian_model.py:197-200,
+// 246-249), which initialises the Gaussian scales from a point cloud.  Same definition: for every point the three
+// smallest squared distances to OTHER points (a duplicate location counts, at distance 0), averaged.  The search
+// runs over the same Morton order + LBVH as the tracer instead of the reference's 1024-point boxes scanned by
+// every thread (O(N^2 / 1024) box tests): a stackless preorder walk pruned by the current third-best distance,
+// seeded by the Morton neighbours.  Arithmetic (shared with the oracle, bit for bit): d2 = fma(dz,dz,fma(dx,dx,dy*dy)),
+// result = ((b0 + b1) + b2) / 3 with b0 <= b1 <= b2.
+// ---------------------------------------------------------------------------------------------------------
+namespace egr {
+
+constexpr uint32_t KNN_FAT = 8;  // subtrees of at most this many points are scanned linearly
+
+__device__ __forceinline__ void knn_update(float (&best)[3], float d2) {
+    if (d2 < best[2]) {
+        best[2] = d2;
+        if (best[2] < best[1]) { const float t = best[1]; best[1] = best[2]; best[2] = t; }
+        if (best[1] < best[0]) { const float t = best[0]; best[0] = best[1]; best[1] = t; }
+    }
+}
+__device__ __forceinline__ float knn_dist2(const float4 a, const f3 p) {
+    const float dx = a.x - p.x, dy = a.y - p.y, dz = a.z - p.z;
+    return fmaf(dz, dz, fmaf(dx, dx, dy * dy));  // the form nvcc contracts the reference's expression into
+}
+
+// leaf boxes (degenerate: the point) + the points in Morton order, then the bottom-up merge
+__global__ void __launch_bounds__(256) k_knn_leaves(BvhView bvh, const float *__restrict__ points) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= bvh.n) return;
+    const uint32_t id = bvh.sorted_ids[j];
+    const f3 p = ld3(points, id);
+    bvh.records[j] = make_float4(p.x, p.y, p.z, __uint_as_float(id));  // compact: one quad per point
+    const uint32_t node = bvh.leaf_node[j];
+    bvh.nodes[2 * (size_t)node] = make_float4(p.x, p.y, p.z, __uint_as_float(node + 1));
+    bvh.nodes[2 * (size_t)node + 1] = make_float4(p.x, p.y, p.z, __uint_as_float(j));
+    merge_boxes_upward(bvh, node);
+}
+
+// one thread per point, in Morton order (the threads of a warp walk nearly the same nodes)
+__global__ void __launch_bounds__(256) k_knn3(BvhView bvh, float *__restrict__ out) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= bvh.n) return;
+    const float4 *__restrict__ pts = bvh.records;
+    const float4 me = pts[j];
+    const f3 p = mk3(me.x, me.y, me.z);
+    float best[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
+    // seed: the Morton neighbours give a bound that prunes most of the tree (they are found again by the walk)
+    const uint32_t lo = j >= 3 ? j - 3 : 0, hi = min(bvh.n - 1, j + 3);
+    for (uint32_t i = lo; i <= hi; ++i)
+        if (i != j) knn_update(best, knn_dist2(pts[i], p));
+    const float bound = best[2];
+    best[0] = best[1] = best[2] = FLT_MAX;
+    const uint32_t end = bvh.num_nodes;
+    uint32_t node = 0;
+    while (node < end) {
+        float4 A, B;
+        ldg2(&bvh.nodes[2 * (size_t)node], A, B);
+        const uint32_t skip = __float_as_uint(A.w), tag = __float_as_uint(B.w);
+        // squared distance from p to the box, rounded DOWN a little: pruning must never drop a closer point
+        const float ex = fmaxf(fmaxf(A.x - p.x, p.x - B.x), 0.0f), ey = fmaxf(fmaxf(A.y - p.y, p.y - B.y), 0.0f),
+                    ez = fmaxf(fmaxf(A.z - p.z, p.z - B.z), 0.0f);
+        const float db = fmaf(ez, ez, fmaf(ey, ey, ex * ex)) * 0.999999f;
+        if (db > bound || db > best[2]) {
+            node = skip;
+            continue;
+        }
+        const uint32_t nl = (skip - node + 1) >> 1;
+        if (nl > KNN_FAT) {
+            node = node + 1;
+            continue;
+        }
+        const uint32_t first = nl == 1 ? tag : (tag & ~FIRST_LEAF_FLAG);
+        for (uint32_t i = first; i < first + nl; ++i)
+            if (i != j) knn_update(best, knn_dist2(pts[i], p));
+        node = skip;
+    }
+    out[__float_as_uint(me.w)] = ((best[0] + best[1]) + best[2]) / 3.0f;
+}
+
+}  // namespace egr
+
+extern "C" size_t egr_knn3_scratch_bytes(uint32_t n) { return align_up(bvh_layout(n).total, 256) + build_scratch_layout(n).total; }
+
+extern "C" int egr_knn3_mean_dist2(const float *points, uint32_t n, float *out, void *scratch, size_t scratch_bytes,
+                                   void *stream) {
+    if (n == 0) return EGR_OK;
+    if (!points || !out) {
+        set_error("egr_knn3_mean_dist2: null points/out");
+        return EGR_EINVAL;
+    }
+    if (n > 0x3fffffffu) {
+        set_error("too many points: %u", n);
+        return EGR_EINVAL;
+    }
+    const size_t need = egr_knn3_scratch_bytes(n);
+    if (!scratch || scratch_bytes < need) {
+        set_error("knn scratch too small: %zu < %zu", scratch_bytes, need);
+        return EGR_ENOMEM;
+    }
+    if ((uintptr_t)scratch & 255u) {
+        set_error("knn scratch must be 256-byte aligned");
+        return EGR_EINVAL;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    BvhView v = bvh_view(scratch, n);
+    const BuildScratch B = build_scratch_layout(n);
+    int rc = build_topology(points, n, v, B, (char *)scratch + align_up(bvh_layout(n).total, 256), st);
+    if (rc) return rc;
+    k_knn_leaves<<<(n + 255) / 256, 256, 0, st>>>(v, points);
+    k_knn3<<<(n + 255) / 256, 256, 0, st>>>(v, out);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}
+
 
 // ---------------------------------------------------------------------------------------------------------
 // Allocation-free rebuild

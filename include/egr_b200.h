@@ -213,6 +213,16 @@ int egr_reset_accumulators(const EgrParams *p, void *stream);
  * driver-resident network, unavailable here; this is the documented pass-through output_final -> output_denoised. */
 int egr_denoise_passthrough(const EgrParams *p, void *stream);
 
+/* ---- next row f3: `distCUDA2` of the reference's simple-knn submodule
+ *      (submodules/simple-knn/simple_knn.cu:46-222, spatial.cu; Python call sites scene/gaussian_model.py:197-200,
+ *      246-249: initial Gaussian scales from a point cloud) --------------------------------------------------
+ * out[i] = mean of the three smallest squared distances from points[i] to OTHER points (duplicates count, at 0;
+ * fewer than four points leave FLT_MAX terms in the sum, as in the reference).  points: [n,3] fp32 device, out: [n]
+ * fp32 device; scratch: caller-owned, egr_knn3_scratch_bytes(n) bytes, 256-byte aligned.  Exact search over the
+ * tracer's Morton order + LBVH; d2 = fma(dz,dz,fma(dx,dx,dy*dy)), result = ((b0 + b1) + b2) / 3. */
+size_t egr_knn3_scratch_bytes(uint32_t n);
+int egr_knn3_mean_dist2(const float *points, uint32_t n, float *out, void *scratch, size_t scratch_bytes, void *stream);
+
 /* Debug/test access: copies of internal arrays (device to device, on `stream`). */
 int egr_bvh_export(const void *storage, size_t storage_bytes, uint32_t num_gaussians, uint32_t *sorted_ids,
                    float *records, float *nodes, uint32_t *parents, void *stream);

@@ -30,6 +30,7 @@
 // Build: g++ -O2 -fopenmp -ffp-contract=off -shared -fPIC (see oracle/Makefile).
 // =============================================================================================
 #include <algorithm>
+#include <cfloat>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -844,3 +845,33 @@ void orc_render(
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------
+// Row f3: mean squared distance to the three nearest neighbours, restating simple-knn's definition
+// (submodules/simple-knn/simple_knn.cu:141-199): for point i the three smallest squared distances to the OTHER
+// points (index != i; duplicates count), kept sorted ascending by the swap cascade of `updateKBest` (:141-154), then
+// (best[0] + best[1] + best[2]) / 3.0f (:198).  Brute force over all pairs (the reference's box pruning only skips
+// points that cannot enter the best three).  The squared distance is the fused form nvcc contracts the reference's
+// `d.x*d.x + d.y*d.y + d.z*d.z` into (SASS of the sm_100 build: FMUL y, FFMA x, FFMA z): fma(dz,dz,fma(dx,dx,dy*dy)) -- fmaf() is correctly rounded, -ffp-contract=off
+// keeps everything else as written.
+// ---------------------------------------------------------------------------------------------------------
+extern "C" void orc_knn3_mean_dist2(const float *points, int n, float *out) {
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int i = 0; i < n; ++i) {
+        const float px = points[3 * i], py = points[3 * i + 1], pz = points[3 * i + 2];
+        float best[3] = {FLT_MAX, FLT_MAX, FLT_MAX};
+        for (int j = 0; j < n; ++j) {
+            if (j == i) continue;
+            const float dx = points[3 * j] - px, dy = points[3 * j + 1] - py, dz = points[3 * j + 2] - pz;
+            float dist = fmaf(dz, dz, fmaf(dx, dx, dy * dy));
+            for (int k = 0; k < 3; ++k) {  // updateKBest<3>
+                if (best[k] > dist) {
+                    const float t = best[k];
+                    best[k] = dist;
+                    dist = t;
+                }
+            }
+        }
+        out[i] = ((best[0] + best[1]) + best[2]) / 3.0f;
+    }
+}

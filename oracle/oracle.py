@@ -133,6 +133,17 @@ def lib():
     return _lib
 
 
+def knn3_mean_dist2(points) -> np.ndarray:
+    """Oracle of ``distCUDA2`` (simple_knn.cu:141-199): brute force, O(N^2); keep N at a few ten thousand."""
+    p = _f32(points).reshape(-1, 3)
+    out = np.zeros(p.shape[0], np.float32)
+    f = lib().orc_knn3_mean_dist2
+    f.argtypes = [_FP, C.c_int, _FP]
+    f.restype = None
+    f(_fp(p), int(p.shape[0]), _fp(out))
+    return out
+
+
 def num_threads() -> int:
     return int(lib().orc_num_threads())
 
@@ -348,3 +359,29 @@ def ref_render(scene, cfg: OrcConfig, cam: OrcCamera, width: int, height: int, t
     if rc != 0:
         raise RuntimeError(f"ref_render failed ({rc}): max_bounces must equal the reference's compile-time value")
     return res
+
+
+# ---- row f3: the reference's own simple-knn compiled in place for sm_100 (oracle/ref_shim/ref_knn.cu) -------
+_REF_KNN_PATH = os.path.join(_HERE, "_ref", "libref_knn.so")
+
+
+def ref_knn_available(try_build: bool = True) -> bool:
+    """True when oracle/_ref/libref_knn.so exists (built here with nvcc from /root/reference, or shipped prebuilt).
+    It is CUDA code: usable on the GPU box only."""
+    if not os.path.exists(_REF_KNN_PATH) and try_build and os.path.isfile(
+            "/root/reference/submodules/simple-knn/simple_knn.cu"):
+        try:
+            subprocess.check_call(["make", "-s", "-C", _HERE, "refknn"])
+        except Exception:
+            return False
+    return os.path.exists(_REF_KNN_PATH)
+
+
+def ref_knn3_mean_dist2(points_dev_ptr: int, n: int, out_dev_ptr: int) -> None:
+    """Run the reference's SimpleKNN::knn on device pointers (synchronises the device)."""
+    L = C.CDLL(_REF_KNN_PATH)
+    L.ref_knn3_mean_dist2.restype = C.c_int
+    L.ref_knn3_mean_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+    rc = L.ref_knn3_mean_dist2(int(n), points_dev_ptr, out_dev_ptr)
+    if rc:
+        raise RuntimeError(f"reference simple-knn failed with CUDA error {rc}")

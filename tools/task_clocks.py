@@ -1,14 +1,15 @@
 """Per-task (32-ray group) durations, node visits and the walk / candidate / rest cycle split of the forward launches.
 Needs the library built with EGR_NVCC_EXTRA=-DEGR_TASK_CLOCKS (the kernels then write %globaltimer stamps and
-counters into the unused tail of the hit-list scratch).  Usage: python tools/task_clocks.py"""
+counters into the tail of the hit log).  Usage: [SCENE=c4] python tools/task_clocks.py"""
 import os, sys
 import numpy as np, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import egr_b200
 from egr_b200 import scenes
-N, R = 1_000_000, 800
+C4 = os.environ.get("SCENE", "c2").lower() == "c4"  # SCENE=c4: the 3M anisotropic set (800x800 here as well)
+N, R = (3_000_000 if C4 else 1_000_000), 800
 dev = torch.device("cuda", 0)
-scene = scenes.kitchen_scene(N, seed=0)
+scene = scenes.catacaustics_scene(N, seed=0) if C4 else scenes.kitchen_scene(N, seed=0)
 cams = scenes.kitchen_cameras(100, R, R)
 pc = scenes.SyntheticModel(scene, device=dev)
 rtr = egr_b200.GaussianRaytracer(pc, R, R, ppll_forward_size=1000, ppll_backward_size=120_000_000)
