@@ -63,6 +63,7 @@ EGR_MAX_STEPS = 8
 EGR_GRAD_STRIDE = 24
 EGR_RECORD_FLOATS = 16
 EGR_NOALLOC_MAX_GAUSSIANS = 65536
+EGR_COMPACT_MAX_ARRAYS = 40
 EGR_PHASE_BEGIN = 0x1
 EGR_PHASE_FINISH = 0x10000
 EGR_PHASE_ALL = 0xFFFFFFFF
@@ -91,6 +92,10 @@ SYMBOLS = {
     "egr_gradients_accumulate": (C.c_int, [_FP, C.c_uint32, C.POINTER(EgrGradTargets), _FP]),
     "egr_knn3_scratch_bytes": (C.c_size_t, [C.c_uint32]),
     "egr_knn3_mean_dist2": (C.c_int, [_FP, C.c_uint32, _FP, _FP, C.c_size_t, _FP]),
+    "egr_prune_keep_mask": (C.c_int, [_FP, C.c_uint32, C.c_float, C.c_float, _FP, _FP]),
+    "egr_compact_scratch_bytes": (C.c_size_t, [C.c_uint32]),
+    "egr_compact_rows": (C.c_int, [_FP, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                   C.POINTER(C.c_uint32), _FP, C.c_size_t, _FP, _FP]),
     "egr_raytrace": (C.c_int, [C.POINTER(EgrParams), C.c_int, _FP]),
     "egr_raytrace_phases": (C.c_int, [C.POINTER(EgrParams), C.c_int, C.c_uint32, _FP]),
     "egr_reset_accumulators": (C.c_int, [C.POINTER(EgrParams), _FP]),

@@ -1,0 +1,111 @@
+// Row f4: pruning mask + stable multi-array compaction (include/egr_b200.h).  Byte/index work, HBM-bound:
+// algorithmic bytes = n (mask) + sum over arrays of (n read-if-kept + kept written) row bytes.
+#include <cub/device/device_scan.cuh>
+#include <cub/iterator/transform_input_iterator.cuh>
+
+#include "egr_common.cuh"
+
+namespace egr {
+
+struct KeepToU32 {
+    __host__ __device__ uint32_t operator()(uint8_t k) const { return k ? 1u : 0u; }
+};
+
+__global__ void __launch_bounds__(256)
+k_prune_keep(const float *__restrict__ tw, uint32_t n, float interval, float min_weight, uint8_t *keep) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) keep[i] = (tw[i] / interval < min_weight) ? 0 : 1;  // train.py:239 (IEEE division, as torch)
+}
+
+struct CompactArrays {
+    const uint32_t *src[EGR_COMPACT_MAX_ARRAYS];
+    uint32_t *dst[EGR_COMPACT_MAX_ARRAYS];
+    uint32_t words[EGR_COMPACT_MAX_ARRAYS];  // 4-byte words per row
+};
+
+// blockIdx.y = array; one thread per 4-byte word of the source, so that reads are fully coalesced and the writes of
+// a run of kept rows are contiguous
+__global__ void __launch_bounds__(256)
+k_compact(const uint8_t *__restrict__ keep, const uint32_t *__restrict__ pos, uint32_t n, CompactArrays a) {
+    const uint32_t w = a.words[blockIdx.y];
+    const size_t total = (size_t)n * w;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t row = (uint32_t)(i / w), k = (uint32_t)(i % w);
+        if (keep[row]) a.dst[blockIdx.y][(size_t)pos[row] * w + k] = a.src[blockIdx.y][i];
+    }
+}
+
+__global__ void k_compact_count(const uint8_t *keep, const uint32_t *pos, uint32_t n, uint32_t *count_out) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) *count_out = pos[n - 1] + (keep[n - 1] ? 1u : 0u);
+}
+
+static size_t scan_temp_bytes(uint32_t n) {
+    size_t b = 0;
+    cub::TransformInputIterator<uint32_t, KeepToU32, const uint8_t *> it(nullptr, KeepToU32());
+    cub::DeviceScan::ExclusiveSum(nullptr, b, it, (uint32_t *)nullptr, (int)n);
+    return b;
+}
+
+}  // namespace egr
+
+using namespace egr;
+
+extern "C" int egr_prune_keep_mask(const float *total_weight, uint32_t n, float interval, float min_weight,
+                                   uint8_t *keep, void *stream) {
+    if (n == 0) return EGR_OK;
+    if (!total_weight || !keep) {
+        set_error("egr_prune_keep_mask: null argument");
+        return EGR_EINVAL;
+    }
+    k_prune_keep<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(total_weight, n, interval, min_weight, keep);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}
+
+extern "C" size_t egr_compact_scratch_bytes(uint32_t n) {
+    return align_up((size_t)n * 4, 256) + align_up(scan_temp_bytes(n), 256);
+}
+
+extern "C" int egr_compact_rows(const uint8_t *keep, uint32_t n, uint32_t num_arrays, const void *const *src,
+                                void *const *dst, const uint32_t *row_bytes, void *scratch, size_t scratch_bytes,
+                                uint32_t *count_out, void *stream) {
+    if (!count_out) {
+        set_error("egr_compact_rows: count_out is null");
+        return EGR_EINVAL;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) {
+        EGR_CUDA_TRY(cudaMemsetAsync(count_out, 0, 4, st));
+        return EGR_OK;
+    }
+    if (!keep || num_arrays > EGR_COMPACT_MAX_ARRAYS || (num_arrays && (!src || !dst || !row_bytes))) {
+        set_error("egr_compact_rows: bad arguments (at most %d arrays)", EGR_COMPACT_MAX_ARRAYS);
+        return EGR_EINVAL;
+    }
+    if (!scratch || scratch_bytes < egr_compact_scratch_bytes(n) || ((uintptr_t)scratch & 255u)) {
+        set_error("egr_compact_rows: scratch too small or not 256-byte aligned (%zu needed)", egr_compact_scratch_bytes(n));
+        return EGR_ENOMEM;
+    }
+    CompactArrays a;
+    for (uint32_t k = 0; k < num_arrays; ++k) {
+        if (!src[k] || !dst[k] || src[k] == dst[k] || row_bytes[k] == 0 || row_bytes[k] % 4 || row_bytes[k] > 64 ||
+            ((uintptr_t)src[k] & 3u) || ((uintptr_t)dst[k] & 3u)) {
+            set_error("egr_compact_rows: array %u: null / aliased / misaligned pointer or row size %u not in {4..64 step 4}",
+                      k, row_bytes[k]);
+            return EGR_EINVAL;
+        }
+        a.src[k] = (const uint32_t *)src[k], a.dst[k] = (uint32_t *)dst[k], a.words[k] = row_bytes[k] / 4;
+    }
+    uint32_t *pos = (uint32_t *)scratch;
+    void *temp = (char *)scratch + align_up((size_t)n * 4, 256);
+    size_t temp_bytes = scan_temp_bytes(n);
+    cub::TransformInputIterator<uint32_t, KeepToU32, const uint8_t *> it(keep, KeepToU32());
+    EGR_CUDA_TRY(cub::DeviceScan::ExclusiveSum(temp, temp_bytes, it, pos, (int)n, st));
+    if (num_arrays) {
+        const uint32_t bx = (uint32_t)min((size_t)148 * 16, ((size_t)n * 16 + 255) / 256);
+        k_compact<<<dim3(bx, num_arrays), 256, 0, st>>>(keep, pos, n, a);
+    }
+    k_compact_count<<<1, 32, 0, st>>>(keep, pos, n, count_out);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}

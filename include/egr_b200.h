@@ -223,6 +223,24 @@ int egr_denoise_passthrough(const EgrParams *p, void *stream);
 size_t egr_knn3_scratch_bytes(uint32_t n);
 int egr_knn3_mean_dist2(const float *points, uint32_t n, float *out, void *scratch, size_t scratch_bytes, void *stream);
 
+/* ---- next row f4: pruning as one stream-ordered pipeline (train.py:238-245 builds the mask
+ *      `total_weight / pruning_interval < min_weight`; scene/gaussian_model.py:479-532 then compacts the 8 parameter
+ *      tensors, their two Adam moments and six side arrays with ~30 separate `tensor[mask]` calls, each of which
+ *      synchronises the host to learn the new size) -----------------------------------------------------------
+ * egr_prune_keep_mask: keep[i] = !(total_weight[i] / interval < min_weight), the complement of the reference's
+ *   prune mask (NaN weights are kept, as `<` is false for them).
+ * egr_compact_rows: stable compaction (== `src[keep]` for every array) of `num_arrays` row-major arrays that share
+ *   the row count n; array a has rows of row_bytes[a] bytes (a multiple of 4, <= 64; base pointers 4-byte aligned).
+ *   dst[a] must not alias src[a] and needs room for n rows; *count_out (device, uint32) receives the number of
+ *   kept rows; the host reads it once to shrink its views.  src/dst/row_bytes are HOST arrays of num_arrays
+ *   (<= EGR_COMPACT_MAX_ARRAYS) entries, read during the call.  scratch: egr_compact_scratch_bytes(n), 256-aligned. */
+#define EGR_COMPACT_MAX_ARRAYS 40
+int egr_prune_keep_mask(const float *total_weight, uint32_t n, float interval, float min_weight, uint8_t *keep,
+                        void *stream);
+size_t egr_compact_scratch_bytes(uint32_t n);
+int egr_compact_rows(const uint8_t *keep, uint32_t n, uint32_t num_arrays, const void *const *src, void *const *dst,
+                     const uint32_t *row_bytes, void *scratch, size_t scratch_bytes, uint32_t *count_out, void *stream);
+
 /* Debug/test access: copies of internal arrays (device to device, on `stream`). */
 int egr_bvh_export(const void *storage, size_t storage_bytes, uint32_t num_gaussians, uint32_t *sorted_ids,
                    float *records, float *nodes, uint32_t *parents, void *stream);
