@@ -24,14 +24,31 @@ struct CompactArrays {
 };
 
 // blockIdx.y = array; one thread per 4-byte word of the source, so that reads are fully coalesced and the writes of
-// a run of kept rows are contiguous
+// a run of kept rows are contiguous.  The row of a word is idx / words-per-row: a compile-time divisor for the row
+// sizes the path has (1, 3, 4 words; 2, 16 for side arrays), 32-bit indices (n * w < 2^32 is checked by the host).
+template <uint32_t W>
+__device__ __forceinline__ void compact_body(const uint8_t *__restrict__ keep, const uint32_t *__restrict__ pos,
+                                             const uint32_t n, const uint32_t *__restrict__ src,
+                                             uint32_t *__restrict__ dst, const uint32_t w_rt) {
+    const uint32_t w = W ? W : w_rt;
+    const uint32_t total = n * w;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const uint32_t row = i / w, k = i - row * w;
+        if (keep[row]) dst[pos[row] * w + k] = src[i];
+    }
+}
 __global__ void __launch_bounds__(256)
 k_compact(const uint8_t *__restrict__ keep, const uint32_t *__restrict__ pos, uint32_t n, CompactArrays a) {
     const uint32_t w = a.words[blockIdx.y];
-    const size_t total = (size_t)n * w;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const uint32_t row = (uint32_t)(i / w), k = (uint32_t)(i % w);
-        if (keep[row]) a.dst[blockIdx.y][(size_t)pos[row] * w + k] = a.src[blockIdx.y][i];
+    const uint32_t *src = a.src[blockIdx.y];
+    uint32_t *dst = a.dst[blockIdx.y];
+    switch (w) {
+    case 1: compact_body<1>(keep, pos, n, src, dst, w); break;
+    case 2: compact_body<2>(keep, pos, n, src, dst, w); break;
+    case 3: compact_body<3>(keep, pos, n, src, dst, w); break;
+    case 4: compact_body<4>(keep, pos, n, src, dst, w); break;
+    case 16: compact_body<16>(keep, pos, n, src, dst, w); break;
+    default: compact_body<0>(keep, pos, n, src, dst, w); break;
     }
 }
 
@@ -85,6 +102,10 @@ extern "C" int egr_compact_rows(const uint8_t *keep, uint32_t n, uint32_t num_ar
     if (!scratch || scratch_bytes < egr_compact_scratch_bytes(n) || ((uintptr_t)scratch & 255u)) {
         set_error("egr_compact_rows: scratch too small or not 256-byte aligned (%zu needed)", egr_compact_scratch_bytes(n));
         return EGR_ENOMEM;
+    }
+    if ((uint64_t)n * 16 > 0xffffffffull) {
+        set_error("egr_compact_rows: too many rows: %u", n);
+        return EGR_EINVAL;
     }
     CompactArrays a;
     for (uint32_t k = 0; k < num_arrays; ++k) {
