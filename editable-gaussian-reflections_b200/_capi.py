@@ -34,6 +34,11 @@ STATS_FIELDS = ["num_accumulated_per_pixel", "num_traversed_per_pixel", "num_hit
                 "num_composited_per_pixel", "num_steps_per_pixel", "hitlog_status"]
 
 EgrCamera = _ptr_struct("EgrCamera", CAMERA_FIELDS)
+class EgrEdit(C.Structure):  # include/egr_b200.h (row f2)
+    _fields_ = [("translate", C.c_float * 3), ("center", C.c_float * 3), ("scale", C.c_float),
+                ("rotation", C.c_float * 9), ("quaternion", C.c_float * 4), ("kill", C.c_int)]
+
+
 GRAD_TARGET_FIELDS = ["mean", "opacity", "scale", "roughness", "rotation", "rgb", "normal", "f0"]
 EgrGradTargets = _ptr_struct("EgrGradTargets", GRAD_TARGET_FIELDS)
 EgrConfig = _ptr_struct("EgrConfig", CONFIG_FIELDS)
@@ -96,6 +101,9 @@ SYMBOLS = {
     "egr_compact_scratch_bytes": (C.c_size_t, [C.c_uint32]),
     "egr_compact_rows": (C.c_int, [_FP, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                    C.POINTER(C.c_uint32), _FP, C.c_size_t, _FP, _FP]),
+    "egr_select_box": (C.c_int, [_FP, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_float), _FP, _FP]),
+    "egr_select_cylinder": (C.c_int, [_FP, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_float), _FP, _FP]),
+    "egr_edit_apply": (C.c_int, [_FP, C.c_uint32, _FP, _FP, _FP, _FP, C.POINTER(EgrEdit), _FP]),
     "egr_raytrace": (C.c_int, [C.POINTER(EgrParams), C.c_int, _FP]),
     "egr_raytrace_phases": (C.c_int, [C.POINTER(EgrParams), C.c_int, C.c_uint32, _FP]),
     "egr_reset_accumulators": (C.c_int, [C.POINTER(EgrParams), _FP]),

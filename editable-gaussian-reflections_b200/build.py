@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libegr_b200.so")
-SOURCES = ["egr_capi.cu", "egr_bvh.cu", "egr_trace.cu", "egr_backward.cu", "egr_prune.cu"]
+SOURCES = ["egr_capi.cu", "egr_bvh.cu", "egr_trace.cu", "egr_backward.cu", "egr_prune.cu", "egr_edit.cu"]
 HEADERS = ["egr_common.cuh", "egr_trace.cuh", os.path.join("..", "..", "include", "egr_b200.h"),
            os.path.join("..", "..", "include", "egr_detmath.h")]
 NVCC_FLAGS = [

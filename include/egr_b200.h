@@ -241,6 +241,35 @@ size_t egr_compact_scratch_bytes(uint32_t n);
 int egr_compact_rows(const uint8_t *keep, uint32_t n, uint32_t num_arrays, const void *const *src, void *const *dst,
                      const uint32_t *row_bytes, void *scratch, size_t scratch_bytes, uint32_t *count_out, void *stream);
 
+/* ---- next row f2: the edit path on the device (scene/editable_gaussian_model.py:30-50 selection
+ *      masks, :201-279 translate / scale / rotate of the selected Gaussians, :324-328 delete; driven by
+ *      gaussian_viewer.py:283-344).  The reference runs N-sized torch / kornia op chains with boolean-mask
+ *      indexing (a host sync each); here one launch per operation, in place, no sync. ---------------------------
+ * egr_select_box:      mask[i] = all(mean[i] - min >= 0) && all(mean[i] - max <= 0)              (:45-48)
+ * egr_select_cylinder: elliptic cylinder inscribed in the box: ((x-cx)/hx)^2 + ((y-cy)/hy)^2 <= 1 and
+ *                      zmin <= z <= zmax, with c = 0.5*(min+max), h = 0.5*(max-min) in fp32       (:30-44)
+ *   `min`/`max` are HOST float[3], read during the call.  mask: device uint8[n] (1 = selected).
+ * egr_edit_apply: for every selected Gaussian, in place (each array may be NULL to skip it):
+ *   mean     <- R*(((mean + t) - oc)*s + oc - oc) + oc with oc = center + t   (:208-236, same op order; the 3x3
+ *               product is an explicit fma chain where the reference calls a GEMM)
+ *   scale    <- log(exp(scale) * s)                                            (:240-254, raw log-scales)
+ *   rotation <- unit(q_edit (x) rotation/|rotation|)  (:256-279 composes rotation MATRICES through kornia and
+ *               converts back: the same rotation, as a unit quaternion that may differ in sign)
+ *   opacity  <- opacity*0 - 1e8 when `kill` != 0                              (:324-328)
+ *   `edit` is a HOST struct read during the call. */
+typedef struct EgrEdit {
+    float translate[3];
+    float center[3];      /* centre of the object's bounding box, 0.5*(min+max) */
+    float scale;          /* uniform */
+    float rotation[9];    /* row-major matrix of the edit rotation (identity for none) */
+    float quaternion[4];  /* the same rotation as a unit quaternion (r,x,y,z) */
+    int kill;
+} EgrEdit;
+int egr_select_box(const float *mean, uint32_t n, const float *min3, const float *max3, uint8_t *mask, void *stream);
+int egr_select_cylinder(const float *mean, uint32_t n, const float *min3, const float *max3, uint8_t *mask, void *stream);
+int egr_edit_apply(const uint8_t *mask, uint32_t n, float *mean, float *scale, float *rotation, float *opacity,
+                   const EgrEdit *edit, void *stream);
+
 /* Debug/test access: copies of internal arrays (device to device, on `stream`). */
 int egr_bvh_export(const void *storage, size_t storage_bytes, uint32_t num_gaussians, uint32_t *sorted_ids,
                    float *records, float *nodes, uint32_t *parents, void *stream);

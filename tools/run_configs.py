@@ -168,7 +168,18 @@ def c5(n5):
         b = ev()
         torch.cuda.synchronize()
         res["selected_fraction"] = float(sel.float().mean())
+        res["select_move_ms_torch_ops"] = a.elapsed_time(b)
+        # the same selection + move through the device edit path (row f2): one launch each, no host sync
+        from egr_b200 import edit
+        pc._xyz[sel] -= torch.tensor([0.1, 0.0, 0.0], device="cuda")  # undo, then redo with the kernels
+        torch.cuda.synchronize()
+        a = ev()
+        m8 = edit.select_box(pc._xyz, (0.5, 0.2, -1e30), (1.5, 1.4, 1.0))
+        edit.apply_edit(m8, mean=pc._xyz, translate=(0.1, 0.0, 0.0), center=(1.0, 0.8, 0.5))
+        b = ev()
+        torch.cuda.synchronize()
         res["select_move_ms"] = a.elapsed_time(b)
+        res["selected_by_kernel_vs_torch"] = [int(m8.sum()), int(sel.sum())]  # (>=,<= vs >,<; undo rounding: boundary points)
         res["move_refit_render_ms"] = render_ms(True)
         a = ev()
         rt.update_bvh()
