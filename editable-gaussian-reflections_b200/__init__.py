@@ -11,6 +11,7 @@ from . import distributed  # noqa: F401
 from .knn import distCUDA2  # noqa: F401
 from . import prune  # noqa: F401
 from . import edit  # noqa: F401
+from . import optim  # noqa: F401
 
 
 def make_raytracer(image_width: int, image_height: int, num_gaussians: int, ppll_forward_size: int = 180_000_000,
@@ -20,4 +21,4 @@ def make_raytracer(image_width: int, image_height: int, num_gaussians: int, ppll
 
 
 __all__ = ["make_raytracer", "Raytracer", "GaussianRaytracer", "render", "scenes", "distributed", "build", "_capi",
-           "DEFAULT_MAX_BOUNCES", "distCUDA2", "prune", "edit"]
+           "DEFAULT_MAX_BOUNCES", "distCUDA2", "prune", "edit", "optim"]

@@ -39,6 +39,12 @@ class EgrEdit(C.Structure):  # include/egr_b200.h (row f2)
                 ("rotation", C.c_float * 9), ("quaternion", C.c_float * 4), ("kill", C.c_int)]
 
 
+class EgrAdam(C.Structure):  # include/egr_b200.h (row f1)
+    _fields_ = [("lr", C.c_double * 8), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double),
+                ("scale_decay", C.c_double), ("step", C.c_uint32), ("clamp", C.c_int), ("zero_grads", C.c_int),
+                ("zero_total_weight", C.c_int)]
+
+
 GRAD_TARGET_FIELDS = ["mean", "opacity", "scale", "roughness", "rotation", "rgb", "normal", "f0"]
 EgrGradTargets = _ptr_struct("EgrGradTargets", GRAD_TARGET_FIELDS)
 EgrConfig = _ptr_struct("EgrConfig", CONFIG_FIELDS)
@@ -104,6 +110,8 @@ SYMBOLS = {
     "egr_select_box": (C.c_int, [_FP, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_float), _FP, _FP]),
     "egr_select_cylinder": (C.c_int, [_FP, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_float), _FP, _FP]),
     "egr_edit_apply": (C.c_int, [_FP, C.c_uint32, _FP, _FP, _FP, _FP, C.POINTER(EgrEdit), _FP]),
+    "egr_adam_step": (C.c_int, [_FP, C.c_uint32, C.POINTER(EgrGradTargets), C.POINTER(EgrGradTargets),
+                                C.POINTER(EgrGradTargets), C.POINTER(EgrAdam), _FP]),
     "egr_raytrace": (C.c_int, [C.POINTER(EgrParams), C.c_int, _FP]),
     "egr_raytrace_phases": (C.c_int, [C.POINTER(EgrParams), C.c_int, C.c_uint32, _FP]),
     "egr_reset_accumulators": (C.c_int, [C.POINTER(EgrParams), _FP]),

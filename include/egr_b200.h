@@ -270,6 +270,30 @@ int egr_select_cylinder(const float *mean, uint32_t n, const float *min3, const 
 int egr_edit_apply(const uint8_t *mask, uint32_t n, float *mean, float *scale, float *rotation, float *opacity,
                    const EgrEdit *edit, void *stream);
 
+/* ---- next row f1: the host step around the tracer as ONE launch.  Reference, per iteration:
+ *      _import_param_gradients (renderer/gaussian_raytracer.py:53-62, 8 add_), the scale decay
+ *      `_scaling = log(exp(_scaling) * scale_decay)` (train.py:224-226), torch.optim.Adam.step over 8 parameter
+ *      groups with eps 1e-15 (scene/gaussian_model.py:333-338; train.py:247), zero_grad of the model and of the
+ *      tracer (train.py:248-249) and three clamps (train.py:251-254): ~30 launches, ~1 GB of elementwise traffic.
+ * egr_adam_step reads the gradient straight from the flat record (96 B), updates the 8 raw parameter arrays and
+ * their two moments in place (Adam without weight decay / amsgrad, bias-corrected as torch does:
+ *   m = m + (1-b1)(g-m); v = b2 v + (1-b2) g g; p -= lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps)),
+ * applies the scale decay to `scale` BEFORE its update when scale_decay < 1, clamps rgb >= 0, roughness and f0 to
+ * [0,1] AFTER the update when `clamp` != 0, and zeroes the record (total_weight column included only when
+ * zero_total_weight != 0; the reference zeroes it every pruning interval, train.py:243).  Arrays of both structs
+ * follow EgrGradTargets' layout; `opt` is a HOST struct read during the call; `step` is the 1-based step count. */
+typedef struct EgrAdam {   /* hyper-parameters are doubles, as the Python floats torch derives its fp32 constants from */
+    double lr[8];         /* order: mean, opacity, scale, roughness, rotation, rgb, normal, f0 */
+    double beta1, beta2, eps;
+    double scale_decay;   /* 1 = none */
+    uint32_t step;
+    int clamp;
+    int zero_grads;
+    int zero_total_weight;
+} EgrAdam;
+int egr_adam_step(float *grad_records, uint32_t count, const EgrGradTargets *params, const EgrGradTargets *exp_avg,
+                  const EgrGradTargets *exp_avg_sq, const EgrAdam *opt, void *stream);
+
 /* Debug/test access: copies of internal arrays (device to device, on `stream`). */
 int egr_bvh_export(const void *storage, size_t storage_bytes, uint32_t num_gaussians, uint32_t *sorted_ids,
                    float *records, float *nodes, uint32_t *parents, void *stream);
