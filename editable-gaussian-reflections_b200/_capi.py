@@ -104,6 +104,7 @@ SYMBOLS = {
     "egr_knn3_scratch_bytes": (C.c_size_t, [C.c_uint32]),
     "egr_knn3_mean_dist2": (C.c_int, [_FP, C.c_uint32, _FP, _FP, C.c_size_t, _FP]),
     "egr_prune_keep_mask": (C.c_int, [_FP, C.c_uint32, C.c_float, C.c_float, _FP, _FP]),
+    "egr_prune_near_cameras": (C.c_int, [_FP, C.c_uint32, _FP, _FP, C.c_uint32, _FP, _FP]),
     "egr_compact_scratch_bytes": (C.c_size_t, [C.c_uint32]),
     "egr_compact_rows": (C.c_int, [_FP, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                    C.POINTER(C.c_uint32), _FP, C.c_size_t, _FP, _FP]),

@@ -17,6 +17,31 @@ k_prune_keep(const float *__restrict__ tw, uint32_t n, float interval, float min
     if (i < n) keep[i] = (tw[i] / interval < min_weight) ? 0 : 1;  // train.py:239 (IEEE division, as torch)
 }
 
+// scene.py:88-105 in one pass: cameras are staged in shared memory 256 at a time, one thread per point
+__global__ void __launch_bounds__(256)
+k_prune_near(const float *__restrict__ mean, uint32_t n, const float *__restrict__ centers,
+             const float *__restrict__ znear, uint32_t nc, uint8_t *keep) {
+    __shared__ float4 cam[256];
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool act = i < n;
+    const float x = act ? mean[3 * (size_t)i] : 0.0f, y = act ? mean[3 * (size_t)i + 1] : 0.0f, z = act ? mean[3 * (size_t)i + 2] : 0.0f;
+    bool near_any = false;
+    for (uint32_t c0 = 0; c0 < nc; c0 += 256) {
+        const uint32_t c = c0 + threadIdx.x;
+        __syncthreads();
+        if (c < nc) cam[threadIdx.x] = make_float4(centers[3 * c], centers[3 * c + 1], centers[3 * c + 2], znear[c]);
+        __syncthreads();
+        const uint32_t m = min(256u, nc - c0);
+        for (uint32_t k = 0; k < m; ++k) {
+            const float dx = __fsub_rn(x, cam[k].x), dy = __fsub_rn(y, cam[k].y), dz = __fsub_rn(z, cam[k].z);
+            // torch's vector norm accumulates the squares in order without contraction
+            const float d = sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)), __fmul_rn(dz, dz)));
+            near_any = near_any || d < cam[k].w;
+        }
+    }
+    if (act && near_any) keep[i] = 0;
+}
+
 struct CompactArrays {
     const uint32_t *src[EGR_COMPACT_MAX_ARRAYS];
     uint32_t *dst[EGR_COMPACT_MAX_ARRAYS];
@@ -75,6 +100,18 @@ extern "C" int egr_prune_keep_mask(const float *total_weight, uint32_t n, float 
         return EGR_EINVAL;
     }
     k_prune_keep<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(total_weight, n, interval, min_weight, keep);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}
+
+extern "C" int egr_prune_near_cameras(const float *mean, uint32_t n, const float *centers, const float *znear,
+                                      uint32_t num_cameras, uint8_t *keep, void *stream) {
+    if (n == 0 || num_cameras == 0) return EGR_OK;
+    if (!mean || !centers || !znear || !keep) {
+        set_error("egr_prune_near_cameras: null argument");
+        return EGR_EINVAL;
+    }
+    k_prune_near<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(mean, n, centers, znear, num_cameras, keep);
     EGR_CUDA_TRY(cudaGetLastError());
     return EGR_OK;
 }

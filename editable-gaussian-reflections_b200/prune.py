@@ -30,6 +30,25 @@ def keep_mask_from_weight(total_weight: torch.Tensor, pruning_interval: float, m
     return keep
 
 
+def drop_near_cameras(keep: torch.Tensor, xyz: torch.Tensor, camera_centers: torch.Tensor, znear: torch.Tensor) -> torch.Tensor:
+    """Clears ``keep[i]`` for every point closer to any camera centre than that camera's ``znear``
+    (``Scene.select_points_to_prune_near_cameras``, scene/scene.py:88-105, one pass instead of one per camera).
+    ``keep``: uint8 [N] (in place), ``xyz`` [N,3], ``camera_centers`` [C,3], ``znear`` [C]: float32 CUDA tensors."""
+    if not (keep.is_cuda and xyz.is_cuda and camera_centers.is_cuda and znear.is_cuda):
+        raise RuntimeError("drop_near_cameras expects CUDA tensors (there is no CPU fallback)")
+    if keep.dtype != torch.uint8 or not keep.is_contiguous() or keep.numel() != xyz.shape[0]:
+        raise RuntimeError("keep must be a contiguous uint8 [N] tensor")
+    x = xyz.detach().to(torch.float32).contiguous()
+    c = camera_centers.detach().to(torch.float32).contiguous().reshape(-1, 3)
+    z = znear.detach().to(torch.float32).contiguous().reshape(-1)
+    if z.numel() != c.shape[0]:
+        raise RuntimeError("one znear per camera centre")
+    with torch.cuda.device(keep.device):
+        _capi.check(_capi.load().egr_prune_near_cameras(x.data_ptr(), x.shape[0], c.data_ptr(), z.data_ptr(), c.shape[0],
+                                                        keep.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    return keep
+
+
 def compact(tensors, keep: torch.Tensor):
     """``[t[keep] for t in tensors]`` for CUDA tensors that share their first dimension, with one launch and one host
     read.  ``keep``: bool or uint8 ``[N]``.  Element sizes must make every row a multiple of 4 bytes (<= 64)."""

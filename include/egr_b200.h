@@ -234,6 +234,12 @@ int egr_knn3_mean_dist2(const float *points, uint32_t n, float *out, void *scrat
  *   dst[a] must not alias src[a] and needs room for n rows; *count_out (device, uint32) receives the number of
  *   kept rows; the host reads it once to shrink its views.  src/dst/row_bytes are HOST arrays of num_arrays
  *   (<= EGR_COMPACT_MAX_ARRAYS) entries, read during the call.  scratch: egr_compact_scratch_bytes(n), 256-aligned. */
+/* egr_prune_near_cameras: keep[i] = 0 for every point closer to ANY camera centre than that camera's znear
+ *   (Scene.select_points_to_prune_near_cameras, scene/scene.py:88-105: one `(points - T).norm(dim=1) < znear`
+ *   pass per training camera, OR-ed); other entries of keep are left as they are.  centers [num_cameras,3] and
+ *   znear [num_cameras] are device fp32 arrays. */
+int egr_prune_near_cameras(const float *mean, uint32_t n, const float *centers, const float *znear,
+                           uint32_t num_cameras, uint8_t *keep, void *stream);
 #define EGR_COMPACT_MAX_ARRAYS 40
 int egr_prune_keep_mask(const float *total_weight, uint32_t n, float interval, float min_weight, uint8_t *keep,
                         void *stream);

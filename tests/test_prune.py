@@ -73,3 +73,28 @@ def test_compaction_rejects_what_it_cannot_do():
         prune.compact([torch.zeros(9, 3, device="cuda")], keep)
     with pytest.raises(RuntimeError):
         prune.compact([torch.zeros(8, 3)], keep)  # host tensor
+
+
+@pytest.mark.gpu
+def test_near_camera_cull_matches_the_per_camera_loop():
+    """scene.py:88-105 run as written (one norm pass per camera, OR-ed) on the same GPU."""
+    import torch
+
+    from egr_b200 import prune
+
+    g = torch.Generator(device="cuda").manual_seed(9)
+    n, nc = 300_007, 301
+    pts = torch.rand(n, 3, device="cuda", generator=g) * 4 - 2
+    centers = torch.rand(nc, 3, device="cuda", generator=g) * 4 - 2
+    znear = torch.rand(nc, device="cuda", generator=g) * 0.12
+    want = torch.zeros(n, dtype=torch.bool, device="cuda")
+    for k in range(nc):
+        want |= (pts - centers[k]).norm(dim=1) < znear[k]
+    assert 100 < int(want.sum()) < n // 2
+    keep = torch.ones(n, dtype=torch.uint8, device="cuda")
+    keep[::5] = 0  # already dropped entries stay dropped
+    prune.drop_near_cameras(keep, pts, centers, znear)
+    expect = torch.ones(n, dtype=torch.bool, device="cuda")
+    expect[::5] = False
+    expect &= ~want
+    assert torch.equal(keep.bool(), expect)
