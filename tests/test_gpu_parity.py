@@ -181,6 +181,35 @@ def test_forward_bounces_and_gradients_pinned(small):
         assert np.abs(refg[k]).max() > 0
 
 
+def test_three_bounces_with_max_bounces_three(small):
+    """BASELINE config C3's setting: the constructor's max_bounces = 3 (four ray steps; the reference compiles
+    MAX_BOUNCES = 2), forward and backward against the oracle pinned to the GPU's rays."""
+    import torch
+
+    sc, cam, W, Hh = small
+    cfg = dict(num_bounces=3, jitter_primary_rays=True, loss_weight_diffuse=5.0, loss_weight_specular=3.0)
+    rt = H.make_gpu_raytracer(sc, cam, cfg, max_bounces=3)
+    assert rt.get_framebuffer().output_rgb.shape[0] == 4 and rt.MAX_BOUNCES() == 3
+    tg = scenes.random_targets(W, Hh, seed=11)
+    H.set_targets(rt, tg)
+    with torch.no_grad():
+        rt.raytrace()
+    out = H.gpu_outputs(rt)
+    ocfg = orc.make_config(max_bounces=3, num_bounces=3, jitter_primary_rays=1, loss_weight_diffuse=5.0,
+                           loss_weight_specular=3.0)
+    ref = _pinned_oracle(rt, sc, cam, W, Hh, ocfg, out, 1)
+    for k in H.OUT_KEYS:
+        assert _buf_err(out[k], ref[k]) <= _tol(k), (k, _buf_err(out[k], ref[k]))
+    assert int(out["num_steps_per_pixel"].max()) == 4 and (out["step_executed"][3] > 0).mean() > 0.05
+    with torch.enable_grad():
+        rt.raytrace()
+    g = H.gpu_grads(rt)
+    out2 = H.gpu_outputs(rt)
+    refg = _pinned_oracle(rt, sc, cam, W, Hh, ocfg, out2, 2, grads=True, targets=tg)
+    for k in list(H.GRAD_MAP) + ["total_weight"]:
+        assert H.rel_err(g[k], refg[k]) <= TOL_GRAD, (k, H.rel_err(g[k], refg[k]))
+
+
 def test_gradients_independent_oracle_primary(small):
     """num_bounces = 0 with a fully independent oracle (own records, own rays): gradients <= 1e-3 relative."""
     import torch
