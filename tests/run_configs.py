@@ -5,10 +5,10 @@
   C3  kitchen scene, 1920x1080, 3 reflection bounces (max_bounces=3), forward only, 16 accumulated calls
   C4  3M anisotropic Gaussians, 1024x768 views sharded over the ranks of a torchrun job (one view per rank per step),
       train iteration with one gradient all-reduce; run as
-      python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 tools/run_configs.py c4
+      python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 tests/run_configs.py c4
   C5  10M Gaussians: bounding-box selection move / delete / duplicate, refit / rebuild + 1080p 3-bounce re-render
 
-Prints one JSON line per config.  Usage: python tools/run_configs.py [c1] [c3] [c4] [c5] [--n5 N]
+Prints one JSON line per config.  Usage: python tests/run_configs.py [c1] [c3] [c4] [c5] [--n5 N]
 """
 import json
 import os
@@ -19,7 +19,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))  # (this file lives in tests/: it is test infrastructure and may use the oracle)
 
 import torch  # noqa: E402
 

@@ -1,6 +1,6 @@
 """BASELINE.json's full size (config C2: 1,000,000 Gaussians, 800x800, 1 bounce) through properties that do not
 need the oracle to finish: determinism, ordering, bounds, linearity of the gradients in the loss weights,
-idempotence of the refit, log capacity.  (The oracle takes ~20 minutes per C2 view; `tools/run_configs.py C1`
+idempotence of the refit, log capacity.  (The oracle takes ~20 minutes per C2 view; `tests/run_configs.py C1`
 and the small-size parity tests cover value parity.)"""
 import numpy as np
 import pytest
