@@ -270,12 +270,21 @@ __global__ void __launch_bounds__(256) k_refit(BvhView bvh, EgrGaussians g, EgrC
     bvh.rawgeo[2 * (size_t)j + 0] = q4;
     bvh.rawgeo[2 * (size_t)j + 1] = make_float4(sraw.x, sraw.y, sraw.z, 0.0f);
 
-    // world box of the image of [-1,1]^3 under M = R diag(S), inflated so that it is strictly conservative w.r.t.
-    // the exact local-space test (which alone defines the candidate set)
+    // World box of the proxy ELLIPSOID, the image of the unit sphere under M = R diag(S): half-extent along axis i =
+    // |row i of M|.  An accepted hit is the point of closest approach and lies inside the unit sphere of the local
+    // frame (shaders.cu:49-52), hence inside this box -- up to sqrt(3) tighter per axis than the box of the image of
+    // [-1,1]^3 for rotated or elongated Gaussians.  (The reference's proxy primitive is the unit BOX; the segment rule
+    // that comes with it, eval_hit's `t < tmin || t > tmax` branch, is why the collection walk culls against the whole
+    // forward ray rather than [tmin, tmax].)  Inflated so that it is strictly conservative w.r.t. the exact test.
     float bmin[3], bmax[3];
 #pragma unroll
     for (int rr = 0; rr < 3; ++rr) {
+#ifdef EGR_HULL_BOXES
         float e = fabsf(R[rr][0]) * S.x + fabsf(R[rr][1]) * S.y + fabsf(R[rr][2]) * S.z;
+#else
+        const float ax = R[rr][0] * S.x, ay = R[rr][1] * S.y, az = R[rr][2] * S.z;
+        float e = sqrtf(fmaf(az, az, fmaf(ay, ay, ax * ax))) * 1.000001f;
+#endif
         e = e * 1.00002f + 1.0e-6f * (fabsf(muv[rr]) + e) + 1.0e-30f;
         bmin[rr] = visible ? muv[rr] - e : 1.0f;
         bmax[rr] = visible ? muv[rr] + e : -1.0f;

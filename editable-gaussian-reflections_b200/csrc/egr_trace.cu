@@ -150,8 +150,11 @@ __device__ __forceinline__ void traverse(
             // component) stays inf instead of turning into inf - inf = NaN, which the min/max below would ignore
             tn = tn * (tn >= 0.0f ? 0.9999996f : 1.0000004f);
             tf = tf * (tf >= 0.0f ? 1.0000004f : 0.9999996f);
-            float lo = PASS0 ? sc.tmin : fmaxf(sc.tmin, w);
-            float hi = PASS0 || L.cnt < LIST_CAP ? sc.tmax : fminf(sc.tmax, L.maxt);
+            // pass 0 culls against the whole forward ray: a hit whose closest approach lies outside [tmin, tmax] is
+            // still accepted when the segment crosses the local unit box (eval_hit), and the leaf boxes bound the
+            // ellipsoid, not that box
+            float lo = PASS0 ? 0.0f : fmaxf(sc.tmin, w);
+            float hi = PASS0 ? FLT_MAX : (L.cnt < LIST_CAP ? sc.tmax : fminf(sc.tmax, L.maxt));
             hit = fmaxf(tn, lo) <= fminf(tf, hi);
         }
         if (!__any_sync(0xffffffffu, hit)) {
@@ -240,8 +243,8 @@ __device__ __forceinline__ void traverse_lane(
                 float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
                 tn = tn * (tn >= 0.0f ? 0.9999996f : 1.0000004f);  // NaN-safe widening, see traverse()
                 tf = tf * (tf >= 0.0f ? 1.0000004f : 0.9999996f);
-                float lo = PASS0 ? sc.tmin : fmaxf(sc.tmin, w);
-                float hi = PASS0 || L.cnt < LIST_CAP ? sc.tmax : fminf(sc.tmax, L.maxt);
+                float lo = PASS0 ? 0.0f : fmaxf(sc.tmin, w);  // see traverse()
+                float hi = PASS0 ? FLT_MAX : (L.cnt < LIST_CAP ? sc.tmax : fminf(sc.tmax, L.maxt));
                 hit = fmaxf(tn, lo) <= fminf(tf, hi);
             }
             if (!hit) {

@@ -210,6 +210,43 @@ def test_three_bounces_with_max_bounces_three(small):
         assert H.rel_err(g[k], refg[k]) <= TOL_GRAD, (k, H.rel_err(g[k], refg[k]))
 
 
+def test_near_and_far_plane_segment_rule_inside_the_cloud():
+    """Camera INSIDE the cloud with a large znear and a small zfar: many Gaussians straddle the planes.  A hit whose
+    closest approach lies outside [znear, zfar] is accepted when the segment crosses the local unit box
+    (shaders.cu proxy-AABB semantics); the leaf boxes only bound the ellipsoid, so the collection walk must not
+    cull by the segment.  Hit counts, ordered ID lists and planes against the pinned brute-force oracle."""
+    import torch
+
+    W, Hh = 40, 30
+    sc = scenes.random_scene(4000, seed=5)
+    sc["scale"] = sc["scale"] + np.float32(0.9)  # larger Gaussians: more of them cross the planes
+    cam = scenes.random_camera(W, Hh, distance=0.35)
+    cam["znear"], cam["zfar"] = 0.45, 1.6
+    cfg = dict(num_bounces=1, jitter_primary_rays=True)
+    rt = H.make_gpu_raytracer(sc, cam, cfg)
+    H.set_targets(rt, scenes.random_targets(W, Hh))
+    with torch.enable_grad():
+        rt.raytrace()
+    out = H.gpu_outputs(rt)
+    ocfg = orc.make_config(num_bounces=1, jitter_primary_rays=1)
+    cap = 128
+    ref = _pinned_oracle(rt, sc, cam, W, Hh, ocfg, out, 1, hit_cap=cap)
+    assert np.array_equal(out["num_hits_per_pixel"], ref["num_hits_per_pixel"])
+    assert np.array_equal(out["num_composited_per_pixel"], ref["num_composited_per_pixel"])
+    assert int(out["num_hits_per_pixel"].sum()) > int(out["num_composited_per_pixel"].sum()) > 1000
+    for step in (0, 1):
+        ids, ts, counts = rt.export_hit_lists(step, cap)
+        assert np.array_equal(counts.cpu().numpy().reshape(Hh, W), ref["hit_counts"][step]), step
+        assert np.array_equal(ids.cpu().numpy().reshape(Hh, W, cap), ref["hit_ids"][step]), step
+    with torch.no_grad():
+        rt.get_metadata().total_num_calls.zero_()
+        rt.raytrace()
+    out = H.gpu_outputs(rt)
+    ref = _pinned_oracle(rt, sc, cam, W, Hh, ocfg, out, 1)
+    for k in ("rgb", "depth", "transmittance", "total_transmittance"):
+        assert _buf_err(out[k], ref[k]) <= TOL_BUF, k
+
+
 def test_gradients_independent_oracle_primary(small):
     """num_bounces = 0 with a fully independent oracle (own records, own rays): gradients <= 1e-3 relative."""
     import torch
