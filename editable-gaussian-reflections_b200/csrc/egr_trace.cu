@@ -844,8 +844,7 @@ static uint32_t resident_blocks() {
     int per_sm_lane = 0;
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_trace_step<false, 4>, 128, 0);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_lane, k_trace_step<true, 1>, 32, 0);
-    (void)per_sm_lane;
-    g_lane_blocks[dev] = (uint32_t)min(sms * per_sm_lane, (int)MAX_RESIDENT_WARPS);
+    g_lane_blocks[dev] = (uint32_t)min(max(1, sms * per_sm_lane), (int)MAX_RESIDENT_WARPS);
     const uint32_t nb = (uint32_t)max(1, sms * per_sm);
     cached[dev] = min(nb, (uint32_t)(MAX_RESIDENT_WARPS / 4));
     return cached[dev];
@@ -935,7 +934,7 @@ extern "C" int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32
             const bool lane_walk = c.force_walk == 2 || (c.force_walk == 0 && s > 0);
             int dev_ = 0;
             cudaGetDevice(&dev_);
-            const uint32_t lane_blocks = min(g_lane_blocks[dev_ & 63], (c.num_warps + 3) / 4 * 4);  // <= hit-list regions
+            const uint32_t lane_blocks = max(1u, min(g_lane_blocks[dev_ & 63], (c.num_warps + 3) / 4 * 4));  // <= hit-list regions
             if (lane_walk) k_trace_step<true, 1><<<lane_blocks, 32, 0, st>>>(c, (int)s, grads_enabled);
             else k_trace_step<false, 4><<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
         }
