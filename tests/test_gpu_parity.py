@@ -210,6 +210,42 @@ def test_three_bounces_with_max_bounces_three(small):
         assert H.rel_err(g[k], refg[k]) <= TOL_GRAD, (k, H.rel_err(g[k], refg[k]))
 
 
+def test_hit_log_overflow_is_flagged_and_contained(small):
+    """A hit log that is too small (the reference's PPLL would overflow silently into foreign memory): the flags
+    are raised, the affected groups get no backward, nothing is written out of bounds, the forward planes of a
+    following no-grad call are unaffected, and a call with enough room clears the per-call flag."""
+    import torch
+
+    sc, cam, W, Hh = small
+    cfg = dict(num_bounces=1, jitter_primary_rays=False, loss_weight_diffuse=5.0)
+    big = H.make_gpu_raytracer(sc, cam, cfg, hit_capacity=4_000_000)
+    H.set_targets(big, scenes.random_targets(W, Hh))
+    with torch.enable_grad():
+        big.raytrace()
+    full = big.get_gaussians().grad_records.clone()
+    chunks_needed = int(big.get_stats().hitlog_status[0])
+    assert chunks_needed > 20 and int(big.get_stats().hitlog_status[1]) == 0
+    with torch.no_grad():
+        big.raytrace()
+    want = H.gpu_outputs(big)["rgb"]
+
+    small_cap = (chunks_needed // 3) * 512  # a third of the chunks the call needs
+    rt = H.make_gpu_raytracer(sc, cam, cfg, hit_capacity=small_cap)
+    H.set_targets(rt, scenes.random_targets(W, Hh))
+    guard = torch.full((1 << 16,), 7.0, device="cuda")  # allocated right after the tracer's buffers
+    with torch.enable_grad():
+        rt.raytrace()
+    st = rt.get_stats().hitlog_status.cpu().numpy()
+    assert st[1] == 1 and st[2] == 1
+    part = rt.get_gaussians().grad_records
+    assert bool(torch.isfinite(part).all()) and float(part.abs().sum()) < float(full.abs().sum())
+    assert float(guard.min()) == 7.0 and float(guard.max()) == 7.0
+    with torch.no_grad():
+        rt.raytrace()
+    assert np.array_equal(H.gpu_outputs(rt)["rgb"], want)  # the forward does not depend on the log
+    assert int(rt.get_stats().hitlog_status[1]) == 0 and int(rt.get_stats().hitlog_status[2]) == 1  # sticky copy stays
+
+
 def test_near_and_far_plane_segment_rule_inside_the_cloud():
     """Camera INSIDE the cloud with a large znear and a small zfar: many Gaussians straddle the planes.  A hit whose
     closest approach lies outside [znear, zfar] is accepted when the segment crosses the local unit box
