@@ -101,6 +101,7 @@ SYMBOLS = {
     "egr_hitlog_bytes_for_hits": (C.c_size_t, [C.c_uint64]),
     "egr_camera_set_pose": (C.c_int, [C.POINTER(EgrCamera), C.POINTER(C.c_float), C.POINTER(C.c_float), _FP]),
     "egr_gradients_accumulate": (C.c_int, [_FP, C.c_uint32, C.POINTER(EgrGradTargets), _FP]),
+    "egr_params_export": (C.c_int, [C.POINTER(EgrGradTargets), C.POINTER(EgrGradTargets), C.c_uint32, _FP]),
     "egr_knn3_scratch_bytes": (C.c_size_t, [C.c_uint32]),
     "egr_knn3_mean_dist2": (C.c_int, [_FP, C.c_uint32, _FP, _FP, C.c_size_t, _FP]),
     "egr_prune_keep_mask": (C.c_int, [_FP, C.c_uint32, C.c_float, C.c_float, _FP, _FP]),

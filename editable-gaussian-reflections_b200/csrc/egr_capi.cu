@@ -53,30 +53,33 @@ extern "C" int egr_camera_set_pose(const EgrCamera *cam, const float *host_origi
 }
 
 namespace egr {
-// one thread per (Gaussian, float4 column group of the record): coalesced 16-byte reads of the record
-__global__ void __launch_bounds__(256) k_grad_accumulate(const float4 *__restrict__ rec, uint32_t n, EgrGradTargets d) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= (size_t)n * (EGR_GRAD_STRIDE / 4)) return;
-    const uint32_t g = (uint32_t)(i / (EGR_GRAD_STRIDE / 4)), q = (uint32_t)(i % (EGR_GRAD_STRIDE / 4));
-    const float4 v = rec[i];
-    auto add3 = [](float *p, size_t k, float x, float y, float z) {
-        if (p) p[3 * k] += x, p[3 * k + 1] += y, p[3 * k + 2] += z;
-    };
-    switch (q) {  // column map: include/egr_b200.h, EgrGaussians
-    case 0: add3(d.mean, g, v.x, v.y, v.z); if (d.opacity) d.opacity[g] += v.w; break;
-    case 1: add3(d.scale, g, v.x, v.y, v.z); if (d.roughness) d.roughness[g] += v.w; break;
-    case 2:
-        if (d.rotation) {
-            float4 *r = reinterpret_cast<float4 *>(d.rotation) + g;
-            float4 o = *r;
-            o.x += v.x, o.y += v.y, o.z += v.z, o.w += v.w;
-            *r = o;
-        }
-        break;
-    case 3: add3(d.rgb, g, v.x, v.y, v.z); break;
-    case 4: add3(d.normal, g, v.x, v.y, v.z); break;
-    default: add3(d.f0, g, v.x, v.y, v.z); break;
+// One block = a tile of 256 Gaussians: the record tile is staged in shared memory with coalesced 16-byte loads, then
+// each destination array is swept with consecutive threads on consecutive elements (all global traffic coalesced).
+constexpr int ACC_TILE = 256;
+template <int CH>
+__device__ __forceinline__ void acc_array(float *D, const float *tile, const int col, const size_t g0, const int ng) {
+    if (!D) return;
+    D += g0 * CH;
+    for (int e = threadIdx.x; e < ng * CH; e += ACC_TILE) {
+        const int gl = e / CH, ch = e - gl * CH;
+        D[e] += tile[gl * EGR_GRAD_STRIDE + col + ch];
     }
+}
+__global__ void __launch_bounds__(ACC_TILE) k_grad_accumulate(const float4 *__restrict__ rec, uint32_t n, EgrGradTargets d) {
+    __shared__ __align__(16) float tile[ACC_TILE * EGR_GRAD_STRIDE];
+    const size_t g0 = (size_t)blockIdx.x * ACC_TILE;
+    const int ng = (int)min((size_t)ACC_TILE, (size_t)n - g0);
+    constexpr int Q = EGR_GRAD_STRIDE / 4;
+    for (int i = threadIdx.x; i < ng * Q; i += ACC_TILE) reinterpret_cast<float4 *>(tile)[i] = rec[g0 * Q + i];
+    __syncthreads();
+    acc_array<3>(d.mean, tile, 0, g0, ng);  // column map: include/egr_b200.h, EgrGaussians
+    acc_array<1>(d.opacity, tile, 3, g0, ng);
+    acc_array<3>(d.scale, tile, 4, g0, ng);
+    acc_array<1>(d.roughness, tile, 7, g0, ng);
+    acc_array<4>(d.rotation, tile, 8, g0, ng);
+    acc_array<3>(d.rgb, tile, 12, g0, ng);
+    acc_array<3>(d.normal, tile, 16, g0, ng);
+    acc_array<3>(d.f0, tile, 20, g0, ng);
 }
 }  // namespace egr
 
@@ -85,13 +88,8 @@ extern "C" int egr_gradients_accumulate(const float *grad_records, uint32_t coun
         egr::set_error("egr_gradients_accumulate: null argument");
         return EGR_EINVAL;
     }
-    if (dst->rotation && ((uintptr_t)dst->rotation & 15u)) {
-        egr::set_error("egr_gradients_accumulate: the rotation target must be 16-byte aligned");
-        return EGR_EINVAL;
-    }
     if (count == 0) return EGR_OK;
-    const size_t threads = (size_t)count * (EGR_GRAD_STRIDE / 4);
-    egr::k_grad_accumulate<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+    egr::k_grad_accumulate<<<(count + egr::ACC_TILE - 1) / egr::ACC_TILE, egr::ACC_TILE, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const float4 *>(grad_records), count, *dst);
     EGR_CUDA_TRY(cudaGetLastError());
     return EGR_OK;
@@ -182,6 +180,51 @@ extern "C" int egr_adam_step(float *grad_records, uint32_t count, const EgrGradT
     c.scale_decay = (float)opt->scale_decay, c.clamp = opt->clamp, c.zero_grads = opt->zero_grads, c.zero_tw = opt->zero_total_weight;
     egr::k_adam_step<<<(count + egr::ADAM_TILE - 1) / egr::ADAM_TILE, egr::ADAM_TILE, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<float4 *>(grad_records), count, *params, *exp_avg, *exp_avg_sq, c);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}
+
+// ---- GaussianRaytracer._export_param_values (renderer/gaussian_raytracer.py:41-51: eight `holder.copy_(param)`) as
+//      one launch: blockIdx.y = array, 16-byte words where alignment allows ------------------------------------------
+namespace egr {
+struct ExportArrays {
+    const float *src[8];
+    float *dst[8];
+    uint32_t floats[8];
+};
+__global__ void __launch_bounds__(256) k_export(ExportArrays a) {
+    const float *s = a.src[blockIdx.y];
+    float *d = a.dst[blockIdx.y];
+    const uint32_t n = a.floats[blockIdx.y];
+    if (!s || !d) return;
+    if ((((uintptr_t)s | (uintptr_t)d) & 15u) == 0) {
+        const uint32_t n4 = n / 4;
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x)
+            reinterpret_cast<float4 *>(d)[i] = reinterpret_cast<const float4 *>(s)[i];
+        for (uint32_t i = n4 * 4 + blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) d[i] = s[i];
+    } else {
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) d[i] = s[i];
+    }
+}
+}  // namespace egr
+
+extern "C" int egr_params_export(const EgrGradTargets *src, const EgrGradTargets *dst, uint32_t count, void *stream) {
+    if (!src || !dst) {
+        egr::set_error("egr_params_export: null argument");
+        return EGR_EINVAL;
+    }
+    if (count == 0) return EGR_OK;
+    if (count > 0x0fffffffu) {
+        egr::set_error("egr_params_export: too many rows: %u", count);
+        return EGR_EINVAL;
+    }
+    static const uint32_t ch[8] = {3, 1, 3, 1, 4, 3, 3, 3};  // EgrGradTargets order
+    egr::ExportArrays a;
+    const float *const *ps = (const float *const *)src;
+    float *const *pd = (float *const *)dst;
+    for (int k = 0; k < 8; ++k) a.src[k] = ps[k], a.dst[k] = pd[k], a.floats[k] = count * ch[k];
+    const unsigned bx = (unsigned)min((size_t)148 * 4, ((size_t)count + 255) / 256);
+    egr::k_export<<<dim3(bx, 8), 256, 0, (cudaStream_t)stream>>>(a);
     EGR_CUDA_TRY(cudaGetLastError());
     return EGR_OK;
 }

@@ -391,6 +391,23 @@ class Raytracer:
         self._build_params()
 
     # ---- test / debug helpers (not in the reference) ---------------------------------------------------------
+    def export_parameters_from(self, sources: dict) -> bool:
+        """holder.copy_(source) for the eight parameters in one launch (egr_params_export).  Returns False without
+        doing anything when a source is not a contiguous float32 CUDA tensor of the holder's shape (the caller then
+        falls back to the reference's eight copy_ calls, gaussian_raytracer.py:41-51)."""
+        g = self.gaussian_data
+        for f in _capi.GRAD_TARGET_FIELDS:
+            s_, d_ = sources.get(f), getattr(g, f)
+            if (s_ is None or not s_.is_cuda or s_.dtype != torch.float32 or not s_.is_contiguous()
+                    or s_.shape != d_.shape or s_.device != d_.device):
+                return False
+        src, dst = _capi.EgrGradTargets(), _capi.EgrGradTargets()
+        for f in _capi.GRAD_TARGET_FIELDS:
+            setattr(src, f, sources[f].data_ptr())
+            setattr(dst, f, getattr(g, f).data_ptr())
+        _capi.check(self._lib.egr_params_export(C.byref(src), C.byref(dst), int(g.count), self._stream()))
+        return True
+
     def accumulate_gradients_into(self, targets: dict):
         """targets[name] += gradient of `name` for the eight parameters, one launch (egr_gradients_accumulate).
         Not in the reference class: its caller does this with eight `add_` (gaussian_raytracer.py:53-62)."""

@@ -206,6 +206,9 @@ typedef struct EgrGradTargets {
     float *mean, *opacity, *scale, *roughness, *rotation, *rgb, *normal, *f0; /* [N,3] [N,1] [N,3] [N,1] [N,4] [N,3] [N,3] [N,3] */
 } EgrGradTargets;
 int egr_gradients_accumulate(const float *grad_records, uint32_t count, const EgrGradTargets *dst, void *stream);
+/* GaussianRaytracer._export_param_values (renderer/gaussian_raytracer.py:41-51: eight `holder.copy_(model tensor)`)
+ * as ONE launch: dst[k] = src[k] for the eight contiguous [N, ch] fp32 arrays (a NULL pair is skipped). */
+int egr_params_export(const EgrGradTargets *src, const EgrGradTargets *dst, uint32_t count, void *stream);
 
 /* FramebufferDataHolder::reset_accumulators (csrc/core/framebuffer.h:249-258) as one launch. */
 int egr_reset_accumulators(const EgrParams *p, void *stream);

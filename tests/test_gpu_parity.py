@@ -492,6 +492,27 @@ def test_fused_gradient_import_equals_eight_adds(small):
     assert torch.equal(part["rgb"], want["rgb"]) and torch.equal(part["rotation"], want["rotation"])
 
 
+def test_fused_parameter_export_equals_eight_copies(small):
+    """egr_params_export (one launch) against the facade's eight copy_ calls; non-conforming sources fall back."""
+    import torch
+
+    sc, cam, W, Hh = small
+    rt = H.make_gpu_raytracer(sc, cam, dict(num_bounces=0))
+    g = rt.get_gaussians()
+    names = ("mean", "opacity", "scale", "roughness", "rotation", "rgb", "normal", "f0")
+    gen = torch.Generator(device="cuda").manual_seed(2)
+    src = {k: torch.randn(getattr(g, k).shape, device="cuda", generator=gen) for k in names}
+    assert rt.export_parameters_from(src) is True
+    for k in names:
+        assert torch.equal(getattr(g, k), src[k]), k
+    before = g.mean.clone()
+    bad = dict(src)
+    bad["mean"] = src["mean"].double()
+    assert rt.export_parameters_from(bad) is False and torch.equal(g.mean, before)
+    bad["mean"] = torch.randn(3001, 3, device="cuda")
+    assert rt.export_parameters_from(bad) is False
+
+
 def test_set_pose_from_host_memory_matches_device_copy(small):
     """A pose held in host tensors goes through egr_camera_set_pose (kernel arguments, no host sync); same bits as
     the device-side copy_ path, including the transposed w2c matrix and partial (mixed host/device) updates."""
