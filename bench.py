@@ -180,10 +180,13 @@ def run_ours(args):
     fb, cam_h = rt.get_framebuffer(), rt.get_camera()
     g = rt.get_gaussians()
 
-    for v in views_dev:  # poses resident on the device too
+    tkeys = (("diffuse", "diffuse_image"), ("specular", "specular_image"), ("depth", "depth_image"),
+             ("normal", "normal_image"), ("f0", "f0_image"), ("roughness", "roughness_image"))
+    for v in views_dev:  # poses resident on the device too; targets resident in the tracer's HWC layout
         Rm = torch.from_numpy(v.R).to(dev)
         v.c2w_dev = -Rm
         v.c2w_dev[:, 0] = -v.c2w_dev[:, 0]
+        v.hwc = {k: getattr(v, attr).moveaxis(0, -1).contiguous() for k, attr in tkeys}
     torch.cuda.synchronize()
 
     def set_view_device(v):
@@ -191,9 +194,8 @@ def run_ours(args):
         with torch.no_grad():
             cam_h.znear.fill_(0.01), cam_h.zfar.fill_(999.9), cam_h.vertical_fov_radians.fill_(v.FoVy)
             cam_h.set_pose(v.camera_center, v.c2w_dev)
-            for k, attr in (("diffuse", "diffuse_image"), ("specular", "specular_image"), ("depth", "depth_image"),
-                            ("normal", "normal_image"), ("f0", "f0_image"), ("roughness", "roughness_image")):
-                getattr(fb, "target_" + k).copy_(getattr(v, attr).moveaxis(0, -1))
+            for k, _ in tkeys:
+                getattr(fb, "target_" + k).copy_(v.hwc[k])
 
     # one event pair per launch where launches are serial; the bounce steps and the backward go in ONE call because
     # the library runs the backward of step s-1 underneath the forward of step s (side stream) within a call
