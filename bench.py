@@ -125,6 +125,10 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1 to its workers; this arm is the one CPU job of the launch and is meant to
+    # use every host core (the OpenMP runtime reads the variable when the oracle library is loaded, below)
+    if os.environ.get("OMP_NUM_THREADS") == "1" and int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     from egr_b200 import scenes
 
     scene = scenes.kitchen_scene(args.num_gaussians, seed=0)
