@@ -66,10 +66,11 @@ class EgrParams(C.Structure):
         ("pixel_state", _FP), ("pixel_state_bytes", C.c_size_t),
         ("hitlog", _FP), ("hitlog_bytes", C.c_size_t),
         ("used_ray_origin", _FP), ("used_ray_direction", _FP), ("step_executed", _FP),
+        ("override_ray_origin", _FP), ("override_ray_direction", _FP), ("override_step_executed", _FP),
     ]
 
 
-EGR_ABI_VERSION = 1
+EGR_ABI_VERSION = 2
 EGR_MAX_STEPS = 8
 EGR_GRAD_STRIDE = 24
 EGR_RECORD_FLOATS = 16

@@ -67,7 +67,11 @@ __device__ __forceinline__ void flush_grads(float *grad_records, uint32_t id, bo
     }
 }
 
-__global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int step) {
+// STEP0: the primary step's loss terms (diffuse, depth, normal, f0, roughness); bounce steps only carry the specular
+// radiance term, so their variant keeps far fewer accumulators live.
+template <bool STEP0>
+__global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int step_arg) {
+    const int step = STEP0 ? 0 : step_arg;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31;
     if (warp >= c.num_warps) return;
@@ -77,7 +81,10 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
     if (step > 0 && warp * 32 >= c.ray_count[step]) return;
     uint32_t pix = 0;
     const bool valid = lane_pixel(c, step, warp, lane, pix);  // same lane <-> ray mapping as the forward of `step`
-    const int nexec = valid ? (int)(c.steps_executed[pix] & 0xFFu) : 0;  // total_effective_steps
+    // What a launch forked under a later forward may read: the backward of step 0 runs on the side stream while the
+    // forward of steps >= 1 writes steps_executed[] and the planes of those steps (egr_trace.cu, egr_raytrace_phases),
+    // so at step 0 it reads neither: every valid pixel executed step 0, and the primary loss needs no bounce radiance.
+    const int nexec = STEP0 ? (valid ? 1 : 0) : (valid ? (int)(c.steps_executed[pix] & 0xFFu) : 0);  // total_effective_steps
     const float exp_power = *cfg.exp_power;
     const float eps_scale_grad = *cfg.eps_scale_grad;
     const float gsf = *cfg.global_scale_factor;
@@ -88,12 +95,17 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
     f3 t_diff = mk3(0, 0, 0), t_spec = mk3(0, 0, 0), t_n = mk3(0, 0, 0), t_f0 = mk3(0, 0, 0);
     float t_depth = 0.0f, t_rough = 0.0f;
     f3 spec = mk3(0, 0, 0);
-    if (valid) {
-        t_diff = ld3(fb.target_diffuse, pix), t_spec = ld3(fb.target_specular, pix);
-        t_n = ld3(fb.target_normal, pix), t_f0 = ld3(fb.target_f0, pix);
-        t_depth = fb.target_depth[pix], t_rough = fb.target_roughness[pix];
-        for (int j = 1; j < B + 1; ++j)  // backward_pass.cu:101-104 (non-executed steps hold zeros)
-            if (j < nexec) spec = spec + plane3(c, SP_RGB, j, pix);
+    if (valid) {  // each step reads only the targets its loss uses (backward_pass.cu:81-108)
+        if (STEP0) {
+            t_diff = ld3(fb.target_diffuse, pix);
+            t_n = ld3(fb.target_normal, pix), t_f0 = ld3(fb.target_f0, pix);
+            t_depth = fb.target_depth[pix], t_rough = fb.target_roughness[pix];
+        } else {
+            t_spec = ld3(fb.target_specular, pix);
+        }
+        if (!STEP0)
+            for (int j = 1; j < B + 1; ++j)  // backward_pass.cu:101-104 (non-executed steps hold zeros)
+                if (j < nexec) spec = spec + plane3(c, SP_RGB, j, pix);
     }
 
     {  // one launch per step, last step first (shaders.cu:157)
@@ -110,7 +122,7 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
         f3 rem_rgb = mk3(0, 0, 0), rem_n = mk3(0, 0, 0), rem_f0 = mk3(0, 0, 0);
         float rem_depth = 0.0f, rem_rough = 0.0f, T_end = 1.0f, T_full = 1.0f;
         if (on) {
-            if (step == 0) {
+            if (STEP0) {
                 d_rgb = 1.0f / 3.0f * sign3(plane3(c, SP_RGB, 0, pix) - t_diff) * *cfg.loss_weight_diffuse;
                 d_depth = sign1(plane(c, SP_DEPTH, 0, pix) - t_depth) * *cfg.loss_weight_depth;
                 d_n = 1.0f / 3.0f * sign3(plane3(c, SP_NORMAL, 0, pix) - t_n) * *cfg.loss_weight_normal;
@@ -123,9 +135,11 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
                 d_rgb = d_rgb * plane3(c, SP_THR, step - 1, pix);
             }
             o = plane3(c, SP_RAY_O, step, pix), d = plane3(c, SP_RAY_D, step, pix);
-            rem_rgb = plane3(c, SP_REM_RGB, step, pix), rem_n = plane3(c, SP_REM_NORMAL, step, pix);
-            rem_f0 = plane3(c, SP_REM_F0, step, pix);
-            rem_depth = plane(c, SP_REM_DEPTH, step, pix), rem_rough = plane(c, SP_REM_ROUGH, step, pix);
+            rem_rgb = plane3(c, SP_REM_RGB, step, pix);
+            if (STEP0) {
+                rem_n = plane3(c, SP_REM_NORMAL, step, pix), rem_f0 = plane3(c, SP_REM_F0, step, pix);
+                rem_depth = plane(c, SP_REM_DEPTH, step, pix), rem_rough = plane(c, SP_REM_ROUGH, step, pix);
+            }
             T_end = plane(c, SP_T, step, pix), T_full = plane(c, SP_TFULL, step, pix);
         }
         const float tmin = step != 0 ? 0.0f : *c.p.camera.znear, tmax = *c.p.camera.zfar;
@@ -135,13 +149,13 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
 
         for (int b = nb - 1; b >= 0; --b) {
             const char *base = (const char *)c.p.hitlog + (size_t)chunk * HITLOG_CHUNK_BYTES;
-            const float4 *entries = (const float4 *)(base + 128);
+            const uint2 *entries = (const uint2 *)(base + 128);
             const uint32_t prev = *(const uint32_t *)base;
             // the log entry of the next slot is fetched one iteration ahead (coalesced, streamed once from HBM)
-            float4 e_next = (b * KBUF + KBUF - 1) < nh ? __ldcs(&entries[(KBUF - 1) * 32 + lane]) : make_float4(0, 0, 0, 0);
+            uint2 e_next = (b * KBUF + KBUF - 1) < nh ? __ldcs(&entries[(KBUF - 1) * 32 + lane]) : make_uint2(0, 0);
             for (int slot = KBUF - 1; slot >= 0; --slot) {
                 const bool has = (b * KBUF + slot) < nh;
-                const float4 e = e_next;
+                const uint2 e = e_next;
                 if (slot > 0 && (b * KBUF + slot - 1) < nh) e_next = __ldcs(&entries[(slot - 1) * 32 + lane]);
                 if (!__any_sync(0xffffffffu, has)) continue;
                 float g[24];
@@ -149,15 +163,16 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
                 for (int k = 0; k < 24; ++k) g[k] = 0.0f;
                 uint32_t id = 0;
                 if (has) {
-                    const uint32_t j = __float_as_uint(e.x);
-                    const float dist = e.y, alpha = e.z, Tr = e.w;
+                    const uint32_t j = e.x;
+                    const float Tr = __uint_as_float(e.y);
                     float4 r0, r1, r2, r3;
                     ldg2(&c.bvh.records[4 * (size_t)j], r0, r1);
                     ldg2(&c.bvh.records[4 * (size_t)j + 2], r2, r3);
-                    float4 q4, s4;  // raw quaternion, raw log-scale as of the last refit (same values as the tensors)
+                    float4 q4, s4;  // raw quaternion; exp(scale), 1/|q| as of the last refit
                     ldg2(&c.bvh.rawgeo[2 * (size_t)j], q4, s4);
                     HitEval h;
-                    eval_hit(r0, r1, r2, r3, o, d, tmin, tmax, exp_power, h);
+                    eval_hit(r0, r1, r2, r3, o, d, tmin, tmax, exp_power, h);  // same bits as the forward's evaluation
+                    const float dist = h.t, alpha = h.alpha;
                     const float sf = r1.w, sigma = r2.w;
                     id = __float_as_uint(r3.w);
                     const float gv = h.gaussval;
@@ -168,7 +183,7 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
                     const float weight = (float)((double)Tr / (1.0 - (double)alpha) * (double)alpha);
                     const f3 g_c = d_rgb * weight;
                     w_rgb = w_rgb + (c_rgb - p_rgb) * Tr, p_rgb = c_rgb;  // backward_pass.cu:117-132
-                    if (step == 0) {
+                    if (STEP0) {
                         const float4 a1 = __ldg(&c.bvh.appearance[3 * (size_t)j + 1]);
                         const float4 a2 = __ldg(&c.bvh.appearance[3 * (size_t)j + 2]);
                         const f3 c_n = mk3(a1.x, a1.y, a1.z), c_f0 = mk3(a2.x, a2.y, a2.z);
@@ -186,16 +201,20 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
                     float dL_da = 0.0f;
                     const float tmp1 = 1.0f / (1.0f - alpha);
                     dL_da += dotp(w_rgb * tmp1, d_rgb);
-                    dL_da += dotp(w_n * tmp1, d_n);
-                    dL_da += dotp(w_f0 * tmp1, d_f0);
-                    dL_da += (w_r * tmp1) * d_rough;
-                    dL_da += (w_d * tmp1) * d_depth;
+                    if (STEP0) {  // the bounce steps' upstream gradients of these channels are zero
+                        dL_da += dotp(w_n * tmp1, d_n);
+                        dL_da += dotp(w_f0 * tmp1, d_f0);
+                        dL_da += (w_r * tmp1) * d_rough;
+                        dL_da += (w_d * tmp1) * d_depth;
+                    }
                     const float tmp2 = -((T_end - T_full) / (1.0f - alpha));
                     dL_da += tmp2 * dotp(rem_rgb, d_rgb);
-                    dL_da += tmp2 * dotp(rem_n, d_n);
-                    dL_da += tmp2 * dotp(rem_f0, d_f0);
-                    dL_da += tmp2 * (rem_rough * d_rough);
-                    dL_da += tmp2 * (rem_depth * d_depth);
+                    if (STEP0) {
+                        dL_da += tmp2 * dotp(rem_n, d_n);
+                        dL_da += tmp2 * dotp(rem_f0, d_f0);
+                        dL_da += tmp2 * (rem_rough * d_rough);
+                        dL_da += tmp2 * (rem_depth * d_depth);
+                    }
                     // opacity (backward_pass.cu:150-152), transform (154-167)
                     float g_op = A_MAX * dL_da * gv;
                     g_op = g_op * sigma * (1.0f - sigma);
@@ -208,9 +227,8 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
                                    sf;
                     const f3 l0 = -dxw.x * h.x, l1 = -dxw.y * h.x, l2 = -dxw.z * h.x;
                     // scale / rotation (backward_pass.cu:169-207) from the raw parameters
-                    const f3 sc_e = mk3(expf(s4.x), expf(s4.y), expf(s4.z));
-                    const float qn = sqrtf(q4.x * q4.x + q4.y * q4.y + q4.z * q4.z + q4.w * q4.w);
-                    const float iqn = 1.0f / qn;
+                    const f3 sc_e = mk3(s4.x, s4.y, s4.z);
+                    const float iqn = s4.w;
                     const float r = q4.x * iqn, xq = q4.y * iqn, yq = q4.z * iqn, zq = q4.w * iqn;
                     const float R00 = 1.f - 2.f * (yq * yq + zq * zq), R01 = 2.f * (xq * yq - r * zq),
                                 R02 = 2.f * (xq * zq + r * yq);
@@ -244,7 +262,7 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
                     g[12] = g_c.x, g[13] = g_c.y, g[14] = g_c.z;
                     g[15] = weight;  // total_weight (backward_pass.cu:220)
                 }
-                if (step == 0) flush_grads<24>(gs.grad_records, id, has, g);
+                if (STEP0) flush_grads<24>(gs.grad_records, id, has, g);
                 else flush_grads<16>(gs.grad_records, id, has, g);
             }
             chunk = prev;
@@ -268,16 +286,22 @@ k_hitlog_export(const TraceCtx c, const int step, const int cap, int32_t *ids, f
     const int nh = (valid && step < nexec && nb > 0) ? __float_as_int(plane(c, SP_NHITS, step, pix)) : 0;
     if (valid) counts[pix] = nh;
     if (nb == 0 || chunk == 0xFFFFFFFFu) return;
+    const f3 o = nh > 0 ? plane3(c, SP_RAY_O, step, pix) : mk3(0, 0, 0), d = nh > 0 ? plane3(c, SP_RAY_D, step, pix) : mk3(0, 0, 1);
+    const float tmin = step != 0 ? 0.0f : *c.p.camera.znear, tmax = *c.p.camera.zfar, exp_power = *c.p.config.exp_power;
     for (int b = nb - 1; b >= 0; --b) {
         const char *base = (const char *)c.p.hitlog + (size_t)chunk * HITLOG_CHUNK_BYTES;
-        const float4 *entries = (const float4 *)(base + 128);
+        const uint2 *entries = (const uint2 *)(base + 128);
         for (int slot = 0; slot < KBUF; ++slot) {
             const int idx = b * KBUF + slot;
             if (idx < nh && idx < cap) {
-                const float4 e = entries[slot * 32 + lane];
-                const uint32_t j = __float_as_uint(e.x);
-                ids[(size_t)pix * cap + idx] = (int32_t)__float_as_uint(c.bvh.records[4 * (size_t)j + 3].w);
-                if (ts) ts[(size_t)pix * cap + idx] = e.y;
+                const uint32_t j = entries[slot * 32 + lane].x;
+                const float4 *rp = &c.bvh.records[4 * (size_t)j];
+                ids[(size_t)pix * cap + idx] = (int32_t)__float_as_uint(rp[3].w);
+                if (ts) {  // the distance is not logged: recomputed exactly as the forward evaluated it
+                    HitEval h;
+                    eval_hit(rp[0], rp[1], rp[2], rp[3], o, d, tmin, tmax, exp_power, h);
+                    ts[(size_t)pix * cap + idx] = h.t;
+                }
             }
         }
         chunk = *(const uint32_t *)base;
@@ -295,7 +319,10 @@ int launch_hitlog_export(const TraceCtx &c, int step, int cap, int32_t *ids, flo
 int launch_backward_impl(const TraceCtx &c, uint32_t step_mask, cudaStream_t st) {
     const uint32_t blocks = (c.num_warps + 3) / 4;
     for (int step = (int)c.S - 1; step >= 0; --step)
-        if (step_mask >> step & 1u) k_backward<<<blocks, 128, 0, st>>>(c, step);
+        if (step_mask >> step & 1u) {
+            if (step == 0) k_backward<true><<<blocks, 128, 0, st>>>(c, 0);
+            else k_backward<false><<<blocks, 128, 0, st>>>(c, step);
+        }
     EGR_CUDA_TRY(cudaGetLastError());
     return EGR_OK;
 }

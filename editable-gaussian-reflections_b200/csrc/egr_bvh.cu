@@ -266,9 +266,10 @@ __global__ void __launch_bounds__(256) k_refit(BvhView bvh, EgrGaussians g, EgrC
     bvh.records[4 * (size_t)j + 1] = make_float4(Wr[0][0], Wr[0][1], Wr[0][2], sf);
     bvh.records[4 * (size_t)j + 2] = make_float4(Wr[1][0], Wr[1][1], Wr[1][2], sigma);
     bvh.records[4 * (size_t)j + 3] = make_float4(Wr[2][0], Wr[2][1], Wr[2][2], __uint_as_float(id));
-    // raw parameters the backward differentiates through, in leaf order next to the record (one dependent gather less)
+    // what the backward differentiates through, in leaf order next to the record (one dependent gather less): the raw
+    // quaternion, and exp(scale) and 1 / |q| as computed here (the backward then needs no exp / sqrt per hit)
     bvh.rawgeo[2 * (size_t)j + 0] = q4;
-    bvh.rawgeo[2 * (size_t)j + 1] = make_float4(sraw.x, sraw.y, sraw.z, 0.0f);
+    bvh.rawgeo[2 * (size_t)j + 1] = make_float4(s.x, s.y, s.z, 1.0f / norm);  // exp(log-scale), 1 / |q|
 
     // World box of the proxy ELLIPSOID, the image of the unit sphere under M = R diag(S): half-extent along axis i =
     // |row i of M|.  An accepted hit is the point of closest approach and lies inside the unit sphere of the local
@@ -358,6 +359,7 @@ extern "C" int egr_bvh_refit(const EgrGaussians *g, const EgrConfig *cfg, void *
         set_error("bvh storage too small: %zu < %zu", storage_bytes, bvh_layout(g->count).total);
         return EGR_ENOMEM;
     }
+    NvtxRange r_("egr:refit");
     BvhView v = bvh_view(storage, g->count);
     k_refit<<<(g->count + 255) / 256, 256, 0, (cudaStream_t)stream>>>(v, *g, *cfg);
     EGR_CUDA_TRY(cudaGetLastError());
@@ -407,6 +409,7 @@ extern "C" int egr_bvh_build(const EgrGaussians *g, const EgrConfig *cfg, void *
         return EGR_ENOMEM;
     }
     cudaStream_t st = (cudaStream_t)stream;
+    NvtxRange r_("egr:rebuild");
     BvhView v = bvh_view(storage, n);
     rc = build_topology(g->mean, n, v, B, (char *)scratch, st);
     if (rc) return rc;

@@ -4,6 +4,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <nvtx3/nvToolsExt.h>
+
 #include "../../include/egr_b200.h"
 #include "../../include/egr_detmath.h"
 
@@ -19,6 +21,15 @@ void set_error(const char *fmt, ...);
             return EGR_ECUDA;                                                                \
         }                                                                                    \
     } while (0)
+
+// NVTX range around a host-side phase (refit, each forward step, the backward): visible to nsys / ncu --nvtx, a
+// no-op without a tool attached.
+struct NvtxRange {
+    explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange &) = delete;
+    NvtxRange &operator=(const NvtxRange &) = delete;
+};
 
 // ---- constants of the reference's flags.h ---------------------------------------------------------------
 constexpr float A_MAX = 0.9999f;            // flags.h:8  MAX_ALPHA
@@ -61,7 +72,7 @@ struct BvhView {
     float *bounds;          // [6] scene bounds of the means (min xyz, max xyz) used for the Morton grid
     uint32_t *sorted_ids;   // [n] leaf j -> Gaussian id
     float4 *records;        // [n][4] geometry record in leaf order (layout: eval_hit below)
-    float4 *rawgeo;         // [n][2] raw quaternion | raw log-scale,_ in leaf order (the backward's second gather by leaf)
+    float4 *rawgeo;         // [n][2] raw quaternion | exp(log-scale), 1/|q| in leaf order (the backward's second gather by leaf)
     float4 *appearance;     // [n][3] activated rgb,rough | normal,_ | f0,_
     float4 *nodes;          // [num_nodes][2]: (bmin.xyz, skip) (bmax.xyz, leaf | FIRST_LEAF_FLAG+first leaf)
     uint32_t *parents;      // [num_nodes] preorder index of the parent
@@ -140,16 +151,19 @@ __host__ __device__ inline StateLayout state_layout(uint32_t w, uint32_t h, uint
     L.warp_off = o, o = align_up(o + (size_t)L.num_warps * S * 4, 256);
     L.ray_count = o, o = align_up(o + (size_t)S * 4, 256);
     L.work_counter = o, o = align_up(o + (size_t)S * 4, 256);
-    // per-resident-warp hit lists of the forward ((64 list + 16 batch) entries x 32 lanes x 8 B = 20 KiB each)
+    // per-resident-warp hit lists of the forward: HITLIST_WARP_BYTES = (LIST_CAP x 32 x (4 + 8) B + KBUF x 32 x 16 B)
+    // = 56 KiB each at LIST_CAP = 128; one region per warp the persistent launches can keep resident (<= 4096, i.e.
+    // up to 224 MiB for images of 800x800 and above; smaller images need one region per 8x4 tile)
     L.hitlist = o, o = align_up(o + (size_t)min_u32(L.num_warps + 3, MAX_RESIDENT_WARPS) * HITLIST_WARP_BYTES, 256);
     L.total = o;
     return L;
 }
 
-// Hit log: one 8 KiB chunk per (warp tile, batch of 16): slot-major [16][32] entries of 16 B
-// {leaf j, t, alpha, T_after} so that the 32 lanes write / read 512 contiguous bytes per slot, + a 128 B header
-// holding the previous chunk of the same warp-step.
-constexpr size_t HITLOG_CHUNK_BYTES = 128 + 16 * 32 * 16;
+// Hit log: one chunk per (32-ray group, batch of 16): slot-major [16][32] entries of 8 B {leaf j, T_after}, so that
+// the 32 lanes write / read 256 contiguous bytes per slot, + a 128 B header holding the previous chunk of the same
+// group-step.  Distance, alpha and the local hit are NOT logged: the backward recomputes them from the geometry
+// record with the same eval_hit the forward used (bit-identical), which halves the log traffic of both passes.
+constexpr size_t HITLOG_CHUNK_BYTES = 128 + 16 * 32 * 8;
 
 // ---- small vector helpers -----------------------------------------------------------------------------------
 struct f3 {

@@ -419,6 +419,10 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
             c.ray_pix[(size_t)step * c.P + r] = pix;
             o = plane3(c, SP_NEXT_O, step - 1, pix);
             d = plane3(c, SP_NEXT_D, step - 1, pix);
+            if (c.p.override_ray_origin) {  // test input: the bounce ray logged by another implementation
+                o = ld3(c.p.override_ray_origin, (size_t)step * c.P + pix);
+                d = ld3(c.p.override_ray_direction, (size_t)step * c.P + pix);
+            }
             seed = c.p.metadata.random_seeds[pix];
         }
     }
@@ -506,7 +510,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
         if (kt[0] == FLT_MAX) done = true;  // forward_pass.cu:80-83
         if (!__any_sync(0xffffffffu, !done)) break;
         // one hit-log chunk per warp per batch (slot-major so that 32 lanes write 512 contiguous bytes)
-        float4 *chunk = nullptr;
+        uint2 *chunk = nullptr;
         if (grads) {
             uint32_t cidx = 0;
             if (lane == 0) cidx = log_ok ? atomicAdd(&c.p.stats.hitlog_status[0], 1u) : 0xFFFFFFFFu;
@@ -517,7 +521,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
             } else {
                 char *base = hitlog + (size_t)cidx * HITLOG_CHUNK_BYTES;
                 if (lane == 0) *(uint32_t *)base = tail_chunk;
-                chunk = (float4 *)(base + 128);
+                chunk = (uint2 *)(base + 128);
                 tail_chunk = cidx;
                 nbatches++;
             }
@@ -554,7 +558,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
                     c_rough = fmaf(a0.w, wt, c_rough);
                     c_depth = fmaf(t, wt, c_depth);
                     T = nextT;
-                    if (chunk) chunk[i * 32 + lane] = make_float4(__uint_as_float(j), t, alpha, T);
+                    if (chunk) chunk[i * 32 + lane] = make_uint2(j, __float_as_uint(T));
                     nh++;
                     if (T < T_thr) {  // forward_pass.cu:131-134
                         w = sc.tmax;
@@ -674,6 +678,8 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
         set_plane3(c, SP_NEXT_D, step, pix, next_d);
         c.steps_executed[pix] = exec_code;
         spawned = (exec_code & 0x100u) != 0;
+        if (c.p.override_step_executed && step + 1 < (int)c.S)
+            spawned = c.p.override_step_executed[(size_t)(step + 1) * c.P + pix] != 0;
         c.p.metadata.random_seeds[pix] = seed;  // shaders.cu:172 (final value after the last executed step)
     }
     // lanes that spawned a ray feed the compaction of the next step
@@ -683,7 +689,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
 
 // Persistent launch: as many blocks as fit on the machine, every warp fetches the next 32-ray group (an 8x4 tile at
 // step 0, 32 compacted rays at a bounce step) from a counter until the step is done; a resident warp owns one hit-list
-// region for its whole life, so the lists of a step occupy a few tens of MB and stay in L2.
+// region (56 KiB) for its whole life; only the rows a ray fills are touched (~20 KiB per warp on C2, ~60-80 MB in all).
 // The bounce launch is compiled for 28 warps per SM (72 registers, a few spilled values): with many bounce rays the
 // extra warps hide more latency (C3: 31.3 -> 28.2 ms per frame); the primary launch keeps 20 warps of 96 registers.
 // The bounce launch uses one-warp blocks: a block's registers are released as soon as its own warp runs out of work,
@@ -822,10 +828,11 @@ static int make_ctx(const EgrParams *p, TraceCtx &c) {
     c.work_counter = (uint32_t *)(sb + L.work_counter);
     c.hitlist = sb + L.hitlist;
     c.P = L.P, c.S = L.S, c.tiles_x = tiles_x(p->image_width), c.num_warps = L.num_warps;
-    {
-        const char *e = getenv("EGR_FORCE_WALK");  // debugging aid: 1 = warp-uniform walk everywhere, 2 = per-lane
-        c.force_walk = e ? atoi(e) : 0;
-    }
+    static const int force_walk_env = [] {  // debugging aid, read once: 1 = warp-uniform walk everywhere, 2 = per-lane
+        const char *e = getenv("EGR_FORCE_WALK");
+        return e ? atoi(e) : 0;
+    }();
+    c.force_walk = force_walk_env;
     c.hitlog_chunks = p->hitlog ? (uint32_t)min((size_t)0x7fffffff, p->hitlog_bytes / HITLOG_CHUNK_BYTES) : 0;
     return EGR_OK;
 }
@@ -904,6 +911,7 @@ extern "C" int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32
         return EGR_EINVAL;
     }
     if (phase_mask & EGR_PHASE_BEGIN) {
+        NvtxRange r_("egr:begin");
         rc = launch_pack_appearance(c.bvh, p->gaussians, st);
         if (rc) return rc;
         k_begin<<<(c.P + 255) / 256, 256, 0, st>>>(c, grads_enabled);
@@ -919,6 +927,9 @@ extern "C" int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32
     uint32_t forked = 0;
     for (uint32_t s = 0; s < c.S; ++s)
         if (phase_mask & EGR_PHASE_STEP(s)) {
+            static const char *const step_names[EGR_MAX_STEPS] = {"egr:trace_step0", "egr:trace_step1", "egr:trace_step2", "egr:trace_step3",
+                                                                  "egr:trace_step4", "egr:trace_step5", "egr:trace_step6", "egr:trace_step7"};
+            NvtxRange r_(step_names[s]);
             if (side && s == 1) {  // the forward of step 0 precedes this launch in stream order (same or earlier call)
                 {
                     std::lock_guard<std::mutex> lock(side->order);
@@ -939,6 +950,7 @@ extern "C" int egr_raytrace_phases(const EgrParams *p, int grads_enabled, uint32
             else k_trace_step<false, 4><<<blocks, 128, 0, st>>>(c, (int)s, grads_enabled);
         }
     if (phase_mask & EGR_PHASE_FINISH) {
+        NvtxRange r_(grads_enabled ? "egr:backward" : "egr:resolve");
         if (grads_enabled) {
             rc = launch_backward_impl(c, ~forked, st);
             if (rc) return rc;

@@ -336,6 +336,10 @@ class Raytracer:
             p.used_ray_origin = fb.debug_ray_origin.data_ptr()
             p.used_ray_direction = fb.debug_ray_direction.data_ptr()
             p.step_executed = fb.debug_step_executed.data_ptr()
+        ov = getattr(self, "_ray_override", None)
+        if ov is not None:
+            p.override_ray_origin, p.override_ray_direction = ov[0].data_ptr(), ov[1].data_ptr()
+            p.override_step_executed = ov[2].data_ptr()
         self._params = p
 
     # ---- methods (raytracer.cpp:81-120) ------------------------------------------------------------------
@@ -345,14 +349,33 @@ class Raytracer:
             self._hitlog = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self._dev)
             self._build_params()
 
+    def _check_bvh_current(self):
+        """resize() changes the Gaussian count; the tree (topology, array offsets) still describes the old count
+        until rebuild_bvh() runs, so refitting or tracing against it would read a foreign layout."""
+        if self._bvh_count != self.gaussian_data.count:
+            raise RuntimeError(f"resize() must be followed by rebuild_bvh(): the BVH was built for {self._bvh_count} "
+                               f"Gaussians, the holders now have {self.gaussian_data.count}")
+
+    def hitlog_overflowed(self, clear: bool = False) -> bool:
+        """True when a grad-mode raytrace() since construction (or the last ``clear``) ran out of hit-log space: the
+        affected 32-ray groups got NO backward (their gradients are missing).  Reads ``stats.hitlog_status[2]`` --
+        a host synchronisation, so call it where one happens anyway (pruning interval, logging, end of a bench)."""
+        st = self.stats_data.hitlog_status
+        over = bool(int(st[2].item()))
+        if over and clear:
+            st[2] = 0
+        return over
+
     def raytrace(self):
         grads = torch.is_grad_enabled()  # metadata.h:29
+        self._check_bvh_current()
         self._ensure_hitlog(grads)
         _capi.check(self._lib.egr_raytrace(C.byref(self._params), int(grads), self._stream()))
 
     def raytrace_phases(self, phase_mask):
         """raytrace() split into its launches (not in the reference; used by bench.py to time single kernels)."""
         grads = torch.is_grad_enabled()
+        self._check_bvh_current()
         self._ensure_hitlog(grads)
         _capi.check(self._lib.egr_raytrace_phases(C.byref(self._params), int(grads), int(phase_mask), self._stream()))
 
@@ -365,6 +388,7 @@ class Raytracer:
 
     def update_bvh(self):
         """Refit (bvh_wrapper.h:32-59): re-pack geometry records and refresh every box; no host sync."""
+        self._check_bvh_current()
         g = self._gaussians_struct()
         cfg = self._config_struct()
         _capi.check(self._lib.egr_bvh_refit(C.byref(g), C.byref(cfg), self._bvh_storage.data_ptr(),
@@ -418,8 +442,22 @@ class Raytracer:
         _capi.check(self._lib.egr_gradients_accumulate(g.grad_records.data_ptr(), int(g.grad_records.shape[0]),
                                                        C.byref(t), self._stream()))
 
+    def set_ray_override(self, ray_origin=None, ray_direction=None, step_executed=None):
+        """Test input: rays of the steps >= 1 ([S,H,W,3] each) and which steps run ([S,H,W] int32), e.g. the bounce
+        rays another implementation logged.  ``None`` removes the override."""
+        if ray_origin is None:
+            self._ray_override = None
+        else:
+            S, Hh, W = self._S, self.height, self.width
+            f = dict(dtype=torch.float32, device=self._dev)
+            self._ray_override = (torch.as_tensor(ray_origin, **f).reshape(S, Hh, W, 3).contiguous(),
+                                  torch.as_tensor(ray_direction, **f).reshape(S, Hh, W, 3).contiguous(),
+                                  torch.as_tensor(step_executed, dtype=torch.int32, device=self._dev).reshape(S, Hh, W).contiguous())
+        self._build_params()
+
     def export_bvh(self):
         """Copies of (sorted_ids [n], records [n,16], nodes [2n-1,8], parents [2n-1])."""
+        self._check_bvh_current()
         n = self.gaussian_data.count
         dev = self._dev
         ids = torch.empty(n, dtype=torch.int32, device=dev)

@@ -39,6 +39,14 @@ class GaussianRaytracer:
 
     @torch.no_grad()
     def rebuild_bvh(self):
+        # train.py calls this every pruning interval, right after the prune's own host reads: the cheapest place to
+        # notice that a backward since the last rebuild ran out of hit-log space (its gradients were dropped)
+        if self.cuda_module.hitlog_overflowed(clear=True):
+            import warnings
+
+            warnings.warn("egr_b200: the backward hit log overflowed since the last rebuild_bvh(); the gradients of the "
+                          "affected pixel tiles were dropped.  Construct the tracer with a larger ppll_backward_size.",
+                          RuntimeWarning, stacklevel=2)
         self.cuda_module.resize(self.pc._xyz.shape[0])
         self._export_param_values()
         self.cuda_module.rebuild_bvh()

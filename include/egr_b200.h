@@ -31,7 +31,7 @@
 extern "C" {
 #endif
 
-#define EGR_ABI_VERSION 1
+#define EGR_ABI_VERSION 2
 #define EGR_MAX_STEPS 8          /* upper bound on MAX_BOUNCES+1 (reference: flags.h:5 fixes MAX_BOUNCES=2) */
 #define EGR_GRAD_STRIDE 24       /* floats per Gaussian in the flat gradient record, see EgrGaussians */
 #define EGR_RECORD_FLOATS 16     /* floats per packed geometry record */
@@ -110,7 +110,10 @@ typedef struct EgrStats {        /* csrc/core/stats.h:3-6 + three extra planes u
     int32_t *num_hits_per_pixel;         /* [H,W] accepted hits, summed over steps */
     int32_t *num_composited_per_pixel;   /* [H,W] composited hits, summed over steps */
     int32_t *num_steps_per_pixel;        /* [H,W] executed ray-steps */
-    uint32_t *hitlog_status;             /* [4]: chunks used, overflow flag, reserved, reserved */
+    uint32_t *hitlog_status;             /* [4]: [0] hit-log chunks used by the last grad-mode call, [1] 1 when that call
+                                          * ran out of hit-log space (the affected 32-ray groups then get NO backward:
+                                          * their gradients are missing), [2] sticky copy of [1] (set by the library,
+                                          * cleared only by the caller; Raytracer.hitlog_overflowed() reads it), [3] unused */
 } EgrStats;
 
 typedef struct EgrParams {       /* csrc/params.h:11-26 */
@@ -132,6 +135,12 @@ typedef struct EgrParams {       /* csrc/params.h:11-26 */
     /* debug planes, may be NULL: the ray traced at each step and whether the step ran ([S,H,W,3] / [S,H,W]) */
     float *used_ray_origin, *used_ray_direction;
     int32_t *step_executed;
+    /* test inputs, may be NULL ([S,H,W,3] / [S,H,W]): when set, the ray of every step >= 1 is read from these planes
+     * instead of the ray spawned by the previous step, and step s+1 of a pixel runs iff override_step_executed[s+1] != 0.
+     * Lets a test feed the bounce rays logged by another implementation (the reference), so that ulp-level
+     * differences in a reflected ray are not amplified by the next step. */
+    const float *override_ray_origin, *override_ray_direction;
+    const int32_t *override_step_executed;
 } EgrParams;
 
 /* ---- library ------------------------------------------------------------------------------------------ */
@@ -210,7 +219,7 @@ int egr_gradients_accumulate(const float *grad_records, uint32_t count, const Eg
  * as ONE launch: dst[k] = src[k] for the eight contiguous [N, ch] fp32 arrays (a NULL pair is skipped). */
 int egr_params_export(const EgrGradTargets *src, const EgrGradTargets *dst, uint32_t count, void *stream);
 
-/* FramebufferDataHolder::reset_accumulators (csrc/core/framebuffer.h:249-258) as one launch. */
+/* FramebufferDataHolder::reset_accumulators (csrc/core/framebuffer.h:249-258): eight stream-ordered memsets. */
 int egr_reset_accumulators(const EgrParams *p, void *stream);
 /* DenoiserWrapper::run (csrc/optix/denoiser_wrapper.h:76-104): the OptiX AI denoiser is a proprietary
  * driver-resident network, unavailable here; this is the documented pass-through output_final -> output_denoised. */

@@ -1,0 +1,152 @@
+"""Value parity at BASELINE.json's own sizes, CUDA path (through the C ABI) against the CPU oracle:
+
+  C1  50,000 random Gaussians, one 256x256 camera, 1 bounce, forward + backward, in full
+  C2  the 1,000,000-Gaussian kitchen scene: (a) a 2048-pixel block of one 800x800 training view, forward planes,
+      hit counts and ordered hit-ID lists of both steps; (b) the same scene through a 64x48 camera, forward +
+      backward, all eight gradient tensors -- the 1 M-deep tree, Morton ties at scale, refill walks and the
+      warp-aggregated gradient flush are all on this path.
+
+Tolerances are BASELINE.json's north_star: hit-ID lists bit-exact, planes <= 1e-4 max-abs (scaled by the plane's
+magnitude for depth), gradients <= 1e-3 relative to the oracle tensor's max-abs.  The oracle here is the fully
+independent one (own geometry records, own rays): nothing is pinned to the GPU's intermediate values.
+"""
+import numpy as np
+import pytest
+
+import helpers as H
+from egr_b200 import scenes
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+TOL_BUF, TOL_GRAD = 1e-4, 1e-3
+LOSS = dict(loss_weight_diffuse=5.0, loss_weight_specular=3.0, loss_weight_depth=2.5, loss_weight_normal=2.5)
+PLANES = ("rgb", "depth", "normal", "f0", "roughness", "transmittance", "total_transmittance")
+
+
+def _buf_err(a, b):
+    return float(np.abs(a - b).max() / max(1.0, float(np.abs(b).max())))
+
+
+def test_c1_full_size_forward_backward_value_parity():
+    import torch
+
+    W = Hh = 256
+    sc = scenes.random_scene(50_000, seed=0)
+    cam = scenes.random_camera(W, Hh)
+    tg = scenes.random_targets(W, Hh, seed=1)
+    cfg = dict(num_bounces=1, jitter_primary_rays=False, **LOSS)
+    rt = H.make_gpu_raytracer(sc, cam, cfg, hit_capacity=40_000_000)
+    H.set_targets(rt, tg)
+    with torch.no_grad():
+        rt.raytrace()
+    out = H.gpu_outputs(rt)
+    ocfg = orc.make_config(num_bounces=1, jitter_primary_rays=0, **LOSS)
+    ref = orc.render(sc, ocfg, H.oracle_camera(cam), W, Hh, total_num_calls=1)
+    assert np.array_equal(out["step_executed"], ref["step_executed"])
+    for k in PLANES + ("ray_origin", "ray_direction", "final"):
+        assert _buf_err(out[k], ref[k]) <= TOL_BUF, (k, _buf_err(out[k], ref[k]))
+    assert np.array_equal(out["num_hits_per_pixel"], ref["num_hits_per_pixel"])
+    assert np.array_equal(out["num_composited_per_pixel"], ref["num_composited_per_pixel"])
+    assert (ref["step_executed"][1] != 0).mean() > 0.2  # the bounce step really runs
+
+    rt.get_metadata().total_num_calls.fill_(1)
+    with torch.enable_grad():
+        rt.raytrace()
+    torch.cuda.synchronize()
+    assert int(rt.get_stats().hitlog_status[1]) == 0
+    g = H.gpu_grads(rt)
+    cap = 96
+    refg = orc.render(sc, ocfg, H.oracle_camera(cam), W, Hh, total_num_calls=2, grads=True, targets=tg, hit_cap=cap)
+    assert refg["hit_counts"].max() <= cap
+    for step in range(2):
+        ids, ts, counts = rt.export_hit_lists(step, cap)
+        assert np.array_equal(counts.cpu().numpy().reshape(Hh, W), refg["hit_counts"][step]), step
+        assert np.array_equal(ids.cpu().numpy().reshape(Hh, W, cap), refg["hit_ids"][step]), step
+        assert np.array_equal(ts.cpu().numpy().reshape(Hh, W, cap), refg["hit_ts"][step]), step
+    for k in list(H.GRAD_MAP) + ["total_weight"]:
+        assert float(np.abs(refg[k]).max()) > 0, k
+        assert H.rel_err(g[k], refg[k]) <= TOL_GRAD, (k, H.rel_err(g[k], refg[k]))
+
+
+N2 = 1_000_000
+
+
+@pytest.fixture(scope="module")
+def kitchen():
+    return scenes.kitchen_scene(N2, seed=0)
+
+
+def test_c2_scene_block_of_a_training_view_value_parity(kitchen):
+    """2048 consecutive pixels of one 800x800 view of the 1 M scene (the block bench.py's CPU leg times)."""
+    import torch
+
+    R = 800
+    cam = scenes.kitchen_cameras(100, R, R)[0]
+    cfg = dict(num_bounces=1, jitter_primary_rays=True, **LOSS)
+    rt = H.make_gpu_raytracer(kitchen, cam, cfg, debug_rays=True, hit_capacity=120_000_000)
+    H.set_targets(rt, scenes.random_targets(R, R, seed=1))
+    pb = (R // 2) * R + R // 4
+    rng = (pb, pb + 2048)
+    with torch.no_grad():
+        rt.raytrace()
+    out = H.gpu_outputs(rt)
+    ocfg = orc.make_config(num_bounces=1, jitter_primary_rays=1, **LOSS)
+    cap = 96
+    ref = orc.render(kitchen, ocfg, H.oracle_camera(cam), R, R, total_num_calls=1, pixel_range=rng, hit_cap=cap)
+    sel = np.zeros(R * R, bool)
+    sel[rng[0]:rng[1]] = True
+    sel = sel.reshape(R, R)
+    assert np.array_equal(out["step_executed"][:, sel], ref["step_executed"][:, sel])
+    assert (ref["step_executed"][1][sel] != 0).mean() > 0.5
+    for k in PLANES + ("ray_origin", "ray_direction"):
+        a, b = out[k][:, sel], ref[k][:, sel]
+        assert _buf_err(a, b) <= TOL_BUF, (k, _buf_err(a, b))
+    assert _buf_err(out["final"][:, sel], ref["final"][:, sel]) <= TOL_BUF
+    assert np.array_equal(out["num_hits_per_pixel"][sel], ref["num_hits_per_pixel"][sel])
+    assert np.array_equal(out["num_composited_per_pixel"][sel], ref["num_composited_per_pixel"][sel])
+    assert ref["num_hits_per_pixel"][sel].mean() > 20  # the closed room: many Gaussians per ray
+    # ordered hit-ID lists need the hit log: one grad-mode call at the same call number
+    rt.get_metadata().total_num_calls.fill_(0)
+    with torch.enable_grad():
+        rt.raytrace()
+    assert int(rt.get_stats().hitlog_status[1]) == 0
+    for step in range(2):
+        ids, ts, counts = rt.export_hit_lists(step, cap)
+        c = counts.cpu().numpy().reshape(R, R)[sel]
+        assert np.array_equal(c, ref["hit_counts"][step][sel]), step
+        assert np.array_equal(ids.cpu().numpy().reshape(R, R, cap)[sel], ref["hit_ids"][step][sel]), step
+        assert c.max() <= cap
+
+
+def test_c2_scene_gradients_through_a_small_camera(kitchen):
+    """The whole 1 M scene (deep tree, every Gaussian a candidate) through a 64x48 camera: forward planes and all
+    eight gradient tensors + total_weight against the full oracle."""
+    import torch
+
+    W, Hh = 64, 48
+    cam = scenes.kitchen_cameras(100, W, Hh)[33]
+    tg = scenes.random_targets(W, Hh, seed=4)
+    cfg = dict(num_bounces=1, jitter_primary_rays=True, **LOSS)
+    rt = H.make_gpu_raytracer(kitchen, cam, cfg, hit_capacity=8_000_000)
+    H.set_targets(rt, tg)
+    with torch.no_grad():
+        rt.raytrace()
+    out = H.gpu_outputs(rt)
+    ocfg = orc.make_config(num_bounces=1, jitter_primary_rays=1, **LOSS)
+    ocam = H.oracle_camera(cam)
+    ref = orc.render(kitchen, ocfg, ocam, W, Hh, total_num_calls=1)
+    for k in PLANES + ("final",):
+        assert _buf_err(out[k], ref[k]) <= TOL_BUF, (k, _buf_err(out[k], ref[k]))
+    assert np.array_equal(out["num_hits_per_pixel"], ref["num_hits_per_pixel"])
+    with torch.enable_grad():
+        rt.raytrace()
+    torch.cuda.synchronize()
+    assert int(rt.get_stats().hitlog_status[1]) == 0
+    g = H.gpu_grads(rt)
+    refg = orc.render(kitchen, ocfg, ocam, W, Hh, total_num_calls=2, grads=True, targets=tg)
+    for k in list(H.GRAD_MAP) + ["total_weight"]:
+        assert float(np.abs(refg[k]).max()) > 0, k
+        assert H.rel_err(g[k], refg[k]) <= TOL_GRAD, (k, H.rel_err(g[k], refg[k]))
+    # the same Gaussians were composited by some ray on both sides (total_weight sums strictly positive weights)
+    assert np.array_equal(g["total_weight"] > 0, refg["total_weight"] > 0)

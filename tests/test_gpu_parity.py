@@ -414,6 +414,27 @@ def test_resize_and_empty_and_ragged():
     assert g.rgb.grad.shape == (257, 3) and g.rgb.grad.data_ptr() == g.dL_drgb.data_ptr()
 
 
+def test_resize_without_rebuild_is_refused(small):
+    """resize() changes the count; the tree still describes the old one until rebuild_bvh(): refit / trace / export
+    must refuse instead of reading a foreign layout."""
+    import torch
+
+    sc, cam, W, Hh = small
+    rt = H.make_gpu_raytracer(sc, cam, dict(num_bounces=0))
+    rt.resize(2000)
+    for call in (rt.update_bvh, rt.raytrace, rt.export_bvh):
+        with pytest.raises(RuntimeError, match="rebuild_bvh"):
+            with torch.no_grad():
+                call()
+    g = rt.get_gaussians()
+    for k in scenes.PARAM_KEYS:
+        getattr(g, k).copy_(torch.from_numpy(sc[k][:2000]))
+    rt.rebuild_bvh()
+    with torch.no_grad():
+        rt.raytrace()
+    assert bool(torch.isfinite(rt.get_framebuffer().output_rgb).all())
+
+
 def test_renderer_facade_train_like_iteration(small):
     """The reference's caller code path (GaussianRaytracer.__call__ / render) end to end, fwd + bwd."""
     import torch
@@ -429,14 +450,28 @@ def test_renderer_facade_train_like_iteration(small):
     with torch.enable_grad():
         egr_b200.render(view, rtr, denoise=False)
     assert float(pc._xyz.grad.abs().max()) > 0 and torch.isfinite(pc._rotation.grad).all()
+    # what the facade delivered into the model's .grad tensors == the oracle's gradients for the same call (pose
+    # conversion, config transfer, parameter export, target upload, refit, trace and gradient import all in between)
+    ocfg = orc.make_config(num_bounces=1, jitter_primary_rays=1, **{k: v for k, v in scenes.DEFAULT_CFG.items()
+                                                                    if k != "exp_power"}, exp_power=3.0)
+    refg = orc.render(sc, ocfg, H.oracle_camera(cam), W, Hh, total_num_calls=1, grads=True, targets=tg)
+    got = dict(dL_dmean=pc._xyz.grad, dL_dopacity=pc._opacity.grad, dL_dscale=pc._scaling.grad,
+               dL_drotation=pc._rotation.grad, dL_drgb=pc._diffuse.grad, dL_dnormal=pc._normal.grad,
+               dL_droughness=pc._roughness.grad, dL_df0=pc._f0.grad)
+    for k, t in got.items():
+        assert H.rel_err(t.cpu().numpy(), refg[k]) <= TOL_GRAD, (k, H.rel_err(t.cpu().numpy(), refg[k]))
     tw = rtr.cuda_module.get_gaussians().total_weight
+    assert H.rel_err(tw.cpu().numpy(), refg["total_weight"]) <= TOL_GRAD
     assert tw.shape == (3000, 1) and float(tw.max()) > 0
     rtr.zero_grad()
     assert float(rtr.cuda_module.get_gaussians().mean.grad.abs().max()) == 0.0
     with torch.no_grad():
         pkg = egr_b200.render(view, rtr, targets_available=False)
     assert pkg.rgb.shape == (3, 3, Hh, W) and pkg.final.shape == (1, 3, Hh, W)
-    assert float(pkg.rgb.abs().max()) > 0
+    ref = orc.render(sc, ocfg, H.oracle_camera(cam), W, Hh, total_num_calls=2)
+    assert _buf_err(pkg.rgb.cpu().numpy(), np.moveaxis(ref["rgb"], -1, 1)) <= TOL_BUF
+    assert _buf_err(pkg.final.cpu().numpy(), np.moveaxis(ref["final"], -1, 1)) <= TOL_BUF
+    assert _buf_err(pkg.depth.cpu().numpy(), np.moveaxis(ref["depth"], -1, 1)) <= TOL_BUF
 
 
 def test_renderer_facade_host_targets_overlapped_upload(small):
@@ -600,6 +635,31 @@ def test_cuda_vs_committed_reference_vectors():
     gr = H.gpu_grads(rt)
     for k in ("dL_dnormal", "dL_df0", "dL_droughness"):
         assert H.rel_err(gr[k], g["ref_" + k]) <= TOL_GRAD, (k, H.rel_err(gr[k], g["ref_" + k]))
+    # Bounce steps: ulp-level differences in a reflected ray are amplified by the next step's sharp Gaussians, so the
+    # rays the reference logged when it finished step s-1 are fed in as the rays of step s (the same pinning
+    # tests/test_oracle_golden.py applies to the oracle).  Then EVERY plane of EVERY step and all eight gradient
+    # tensors + total_weight are compared with the reference's own numbers.
+    S = 3
+    ro = np.concatenate([out["used_ray_origin"][:1], g["ref_ray_origin"][:-1]])
+    rd = np.concatenate([out["used_ray_direction"][:1], g["ref_ray_direction"][:-1]])
+    ex = np.concatenate([np.ones((1, Hh, W), np.int32), (np.abs(g["ref_ray_direction"][:-1]).sum(-1) > 0).astype(np.int32)])
+    rt.set_ray_override(ro, rd, ex)
+    rt.get_metadata().total_num_calls.fill_(6)
+    with torch.no_grad():
+        rt.raytrace()
+    pinned = H.gpu_outputs(rt)
+    assert np.array_equal(pinned["step_executed"], ex)
+    for k in H.OUT_KEYS:
+        assert _buf_err(pinned[k], g["ref_" + k]) <= _tol(k), (k, _buf_err(pinned[k], g["ref_" + k]))
+    assert (ex[1] != 0).mean() > 0.2 and (ex[2] != 0).mean() > 0.03  # first and second bounces fire
+    rt.get_gaussians().grad_records.zero_()
+    rt.get_metadata().total_num_calls.fill_(6)
+    with torch.enable_grad():
+        rt.raytrace()
+    gr = H.gpu_grads(rt)
+    for k in list(H.GRAD_MAP) + ["total_weight"]:
+        assert H.rel_err(gr[k], g["ref_" + k]) <= TOL_GRAD, (k, H.rel_err(gr[k], g["ref_" + k]))
+    rt.set_ray_override(None)
 
 
 def test_long_rays_beyond_the_hit_list():

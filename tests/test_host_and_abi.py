@@ -48,7 +48,7 @@ def test_struct_layout_matches_header():
     assert C.sizeof(_capi.EgrFramebuffer) == 25 * 8
     assert C.sizeof(_capi.EgrGaussians) == 8 + 9 * 8
     assert C.sizeof(_capi.EgrMetadata) == 3 * 8 and C.sizeof(_capi.EgrStats) == 6 * 8
-    assert C.sizeof(_capi.EgrParams) == 16 + (6 + 20 + 25 + 10 + 3 + 6) * 8 + 6 * 8 + 3 * 8
+    assert C.sizeof(_capi.EgrParams) == 16 + (6 + 20 + 25 + 10 + 3 + 6) * 8 + 6 * 8 + 3 * 8 + 3 * 8  # ... + 3 debug outputs + 3 test inputs
 
 
 def test_size_queries_and_argument_errors_without_gpu():
@@ -57,7 +57,7 @@ def test_size_queries_and_argument_errors_without_gpu():
     per = (lib.egr_bvh_storage_bytes(2_000_000) - lib.egr_bvh_storage_bytes(1_000_000)) / 1e6
     assert 64 + 32 + 48 + 64 + 4 * 4 <= per <= 240  # records + raw geometry + appearance + 2 nodes + index arrays per Gaussian
     assert lib.egr_pixel_state_bytes(800, 800, 3) >= 40 * 3 * 640000 * 4
-    assert lib.egr_hitlog_bytes_for_hits(512) == 128 + 16 * 32 * 16
+    assert lib.egr_hitlog_bytes_for_hits(512) == 128 + 16 * 32 * 8  # {leaf, T_after} per logged hit
     assert lib.egr_raytrace(None, 0, None) == -1 and b"null" in lib.egr_last_error()
     g = _capi.EgrGaussians()
     g.count = 5
