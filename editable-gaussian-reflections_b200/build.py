@@ -12,7 +12,10 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
-LIB_PATH = os.path.join(CSRC, "libegr_b200.so")
+# EGR_B200_LIB: load an already built variant of the library instead (kernel experiments: a second build of the same
+# sources with other -D switches, see tools/build_variant.py); it is never rebuilt automatically.
+_LIB_OVERRIDE = os.environ.get("EGR_B200_LIB")
+LIB_PATH = _LIB_OVERRIDE or os.path.join(CSRC, "libegr_b200.so")
 SOURCES = ["egr_capi.cu", "egr_bvh.cu", "egr_trace.cu", "egr_backward.cu", "egr_prune.cu", "egr_edit.cu"]
 HEADERS = ["egr_common.cuh", "egr_trace.cuh", os.path.join("..", "..", "include", "egr_b200.h"),
            os.path.join("..", "..", "include", "egr_detmath.h")]
@@ -30,23 +33,35 @@ def _nvcc() -> str:
 
 
 def needs_build() -> bool:
+    if _LIB_OVERRIDE:
+        return False
     if not os.path.exists(LIB_PATH):
         return True
     t = os.path.getmtime(LIB_PATH)
     return any(os.path.getmtime(os.path.join(CSRC, f)) > t for f in SOURCES + HEADERS)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, out: str | None = None, extra_flags=()) -> str:
+    """``out`` / ``extra_flags``: build a variant (other -D switches) to another path, objects kept apart."""
+    if out is not None:
+        return _build_to(out, list(extra_flags), verbose)
+    if _LIB_OVERRIDE:
+        return LIB_PATH
     if not force and not needs_build():
         return LIB_PATH
+    return _build_to(LIB_PATH, [], verbose)
+
+
+def _build_to(lib_path: str, extra_flags, verbose: bool) -> str:
     nvcc = _nvcc()
-    objdir = os.path.join(CSRC, "build")
+    tag = "" if lib_path == os.path.join(CSRC, "libegr_b200.so") else "_" + os.path.basename(lib_path).replace(".so", "")
+    objdir = os.path.join(CSRC, "build" + tag)
     os.makedirs(objdir, exist_ok=True)
     objs = []
     procs = []
     for src in SOURCES:
         obj = os.path.join(objdir, src.replace(".cu", ".o"))
-        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc, *NVCC_FLAGS, *extra_flags, "-c", os.path.join(CSRC, src), "-o", obj]
         if verbose:
             print(" ".join(cmd), file=sys.stderr)
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
@@ -55,9 +70,9 @@ def build(force: bool = False, verbose: bool = False) -> str:
         out, _ = pr.communicate()
         if pr.returncode != 0:
             raise RuntimeError(f"nvcc failed on {src}:\n{out.decode(errors='replace')}")
-    cmd = [nvcc, "-shared", "-o", LIB_PATH, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-ldl"]
+    cmd = [nvcc, "-shared", "-o", lib_path, *objs, "-gencode", "arch=compute_100a,code=sm_100a", "-ldl"]
     subprocess.check_call(cmd)
-    return LIB_PATH
+    return lib_path
 
 
 if __name__ == "__main__":

@@ -38,7 +38,7 @@ for vi in (17,):
         pct("step0 " + k, res[0][k]); pct("step1 " + k, res[1][k] - res[0][k])
     ps = rt._pixel_state
     hl = rt._hitlog  # the stamps live in the last 512 chunks of the hit log (egr_trace.cu, EGR_TASK_CLOCKS)
-    CH = 8320
+    CH = 128 + 16 * 32 * 8  # HITLOG_CHUNK_BYTES
     off = (hl.numel() // CH - 512) * CH
     ps = hl
     dbg2 = ps[off + 65536 * 16: off + 65536 * 16 + 2 * 32768 * 16].view(torch.int32).cpu().numpy().astype(np.int64).reshape(2, 32768, 4) & 0xFFFFFFFF
