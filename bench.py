@@ -30,6 +30,31 @@ sys.path.insert(0, ROOT)
 
 METRIC = "Mrays/s fwd+bwd (1-bounce, 1M Gaussians)"
 WORKLOAD = "C2 kitchen-1M: 1,000,000 Gaussians, 800x800 views, train iteration (refit+fwd+bwd), 1 bounce"
+# --config: the driver's line is C2 (BASELINE.json configs[1], the one `metric` is quoted on); C3 / C4 run the same
+# machinery on the other named shapes (BASELINE.json configs[2] / configs[3]) and label their lines accordingly.
+CONFIGS = {
+    "c2": dict(metric=METRIC, workload=WORKLOAD, scene="kitchen", n=1_000_000, w=800, h=800, bounces=1, grads=True,
+               max_bounces=2),
+    "c3": dict(metric="Mrays/s forward (3-bounce, 1M Gaussians, 1920x1080)",
+               workload="C3 novel-view 1080p: 1,000,000 Gaussians (spread opacities), 1920x1080, 3 reflection bounces, "
+                        "forward only (render.py / measure_fps.py)",
+               scene="kitchen_varied", n=1_000_000, w=1920, h=1080, bounces=3, grads=False, max_bounces=3),
+    "c4": dict(metric="Mrays/s fwd+bwd (1-bounce, 3M anisotropic Gaussians)",
+               workload="C4 catacaustics-3M: 3,000,000 anisotropic Gaussians, 1024x768 views, train iteration "
+                        "(refit+fwd+bwd), 1 bounce, views sharded over ranks",
+               scene="catacaustics", n=3_000_000, w=1024, h=768, bounces=1, grads=True, max_bounces=2),
+}
+
+
+def make_scene(kind, n):
+    from egr_b200 import scenes
+
+    if kind == "catacaustics":
+        return scenes.catacaustics_scene(n, seed=0)
+    sc = scenes.kitchen_scene(n, seed=0)
+    if kind == "kitchen_varied":  # a scene that has seen some optimisation: non-uniform opacities so that rays terminate
+        sc["opacity"] = np.random.default_rng(4).uniform(-1.0, 4.0, (n, 1)).astype(np.float32)
+    return sc
 
 
 def _peaks():
@@ -131,8 +156,8 @@ def run_reference(args):
         os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
     from egr_b200 import scenes
 
-    scene = scenes.kitchen_scene(args.num_gaussians, seed=0)
-    cams = scenes.kitchen_cameras(100, args.res, args.res)
+    scene = scenes.kitchen_scene(args.num_gaussians or 1_000_000, seed=0)
+    cams = scenes.kitchen_cameras(100, args.res or 800, args.res or 800)
     n_pix = args.cpu_pixels
     vals = []
     for i in range(args.warmup + args.steps):
@@ -170,19 +195,25 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     peak_gbs, peak_kind = _peaks()
 
-    N, R = args.num_gaussians, args.res
-    scene = scenes.kitchen_scene(N, seed=0)
-    cams = scenes.kitchen_cameras(100, R, R)
+    cf = CONFIGS[args.config]
+    N = args.num_gaussians or cf["n"]
+    Wd, Hd = (args.res, args.res) if args.res else (cf["w"], cf["h"])
+    P = Wd * Hd
+    NB, GRADS = cf["bounces"], cf["grads"]
+    scene = make_scene(cf["scene"], N)
+    cams = scenes.kitchen_cameras(100, Wd, Hd)
     n_tg = 4
-    targets = [scenes.random_targets(R, R, seed=1 + i) for i in range(n_tg)]
+    targets = [scenes.random_targets(Wd, Hd, seed=1 + i) for i in range(n_tg)] if GRADS else [None] * n_tg
     pc = scenes.SyntheticModel(scene, device=dev)
     views_dev = [scenes.SyntheticCamera(cams[i], targets[i % n_tg], device=dev) for i in range(len(cams))]
-    rtr = egr_b200.GaussianRaytracer(pc, R, R, ppll_forward_size=1000, ppll_backward_size=args.hitlog_hits)
+    rtr = egr_b200.GaussianRaytracer(pc, Wd, Hd, ppll_forward_size=1000, ppll_backward_size=args.hitlog_hits,
+                                     max_bounces=cf["max_bounces"])
     rt = rtr.cuda_module
-    rt.get_config().num_bounces.fill_(1)
+    rt.get_config().num_bounces.fill_(NB)
     S = rt._S
     fb, cam_h = rt.get_framebuffer(), rt.get_camera()
     g = rt.get_gaussians()
+    grad_ctx = torch.enable_grad if GRADS else torch.no_grad
 
     tkeys = (("diffuse", "diffuse_image"), ("specular", "specular_image"), ("depth", "depth_image"),
              ("normal", "normal_image"), ("f0", "f0_image"), ("roughness", "roughness_image"))
@@ -190,7 +221,7 @@ def run_ours(args):
         Rm = torch.from_numpy(v.R).to(dev)
         v.c2w_dev = -Rm
         v.c2w_dev[:, 0] = -v.c2w_dev[:, 0]
-        v.hwc = {k: getattr(v, attr).moveaxis(0, -1).contiguous() for k, attr in tkeys}
+        v.hwc = {k: getattr(v, attr).moveaxis(0, -1).contiguous() for k, attr in tkeys} if GRADS else {}
     torch.cuda.synchronize()
 
     def set_view_device(v):
@@ -198,36 +229,41 @@ def run_ours(args):
         with torch.no_grad():
             cam_h.znear.fill_(0.01), cam_h.zfar.fill_(999.9), cam_h.vertical_fov_radians.fill_(v.FoVy)
             cam_h.set_pose(v.camera_center, v.c2w_dev)
-            for k, _ in tkeys:
+            for k in v.hwc:
                 getattr(fb, "target_" + k).copy_(v.hwc[k])
 
-    # one event pair per launch where launches are serial; the bounce steps and the backward go in ONE call because
-    # the library runs the backward of step s-1 underneath the forward of step s (side stream) within a call
+    # one event pair per launch where launches are serial; with gradients the bounce steps and the backward go in ONE
+    # call because the library runs the backward of step s-1 underneath the forward of step s (side stream) within a call
     rest = _capi.EGR_PHASE_FINISH
     for s in range(1, S):
         rest |= _capi.EGR_PHASE_STEP(s)
-    phases = [("begin", _capi.EGR_PHASE_BEGIN), ("trace_step0", _capi.EGR_PHASE_STEP(0)), ("bounce+backward", rest)]
+    if GRADS:
+        phases = [("begin", _capi.EGR_PHASE_BEGIN), ("trace_step0", _capi.EGR_PHASE_STEP(0)), ("bounce+backward", rest)]
+    else:
+        phases = ([("begin", _capi.EGR_PHASE_BEGIN)] + [(f"trace_step{s}", _capi.EGR_PHASE_STEP(s)) for s in range(NB + 1)] +
+                  [("resolve", _capi.EGR_PHASE_FINISH)])
     rays_dev = torch.zeros((), dtype=torch.int64, device=dev)
 
     def new_pair():
         return torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
     def hot_step(view_idx, events=None):
-        """refit + forward + backward of one resident view (+ the gradient all-reduce when world > 1).
+        """refit + forward (+ backward) of one resident view (+ the gradient all-reduce when world > 1).
         `events`: pre-created {phase: (start, end)} pairs recorded around every launch of this step."""
-        with torch.enable_grad():
-            if events is not None:
-                events["refit"][0].record()
-            rt.update_bvh()
-            if events is not None:
-                events["refit"][1].record()
+        with grad_ctx():
+            if GRADS:  # the reference refits in grad mode only (gaussian_raytracer.py:139-140)
+                if events is not None:
+                    events["refit"][0].record()
+                rt.update_bvh()
+                if events is not None:
+                    events["refit"][1].record()
             for name, mask in phases:
                 if events is not None:
                     events[name][0].record()
                 rt.raytrace_phases(mask)
                 if events is not None:
                     events[name][1].record()
-        if world > 1:
+        if world > 1 and GRADS:
             if events is not None:
                 events["allreduce"][0].record()
             distributed.allreduce_gradients(g.grad_records)
@@ -254,7 +290,7 @@ def run_ours(args):
     if clock:
         clock.start()
     sync()
-    names = ["refit"] + [n for n, _ in phases] + (["allreduce"] if world > 1 else [])
+    names = (["refit"] if GRADS else []) + [n for n, _ in phases] + (["allreduce"] if world > 1 and GRADS else [])
     ev_steps = [{n: new_pair() for n in names} for _ in range(K)]  # created before the timed region
     t_a, t_b = new_pair()
     t_a.record()
@@ -279,78 +315,94 @@ def run_ours(args):
     # ---------------- roofline of the slowest kernel ----------------
     roofline = None
     if rank == 0:
+        hh, cc = [], []  # accepted / composited hits of each step (cumulative stats planes, read step by step)
         with torch.no_grad():
             v = views_dev[my_views[Wm + K - 1]]
             set_view_device(v)
             st = rt.get_stats()
-            rt.get_config().num_bounces.fill_(0)
-            rt.raytrace()
-            h0, c0 = int(st.num_hits_per_pixel.sum().item()), int(st.num_composited_per_pixel.sum().item())
-            rt.get_config().num_bounces.fill_(1)
-            rt.get_metadata().total_num_calls.sub_(1)
-            rt.raytrace()
-            h1 = int(st.num_hits_per_pixel.sum().item()) - h0
-            c1 = int(st.num_composited_per_pixel.sum().item()) - c0
-        P = R * R
+            calls0 = rt.get_metadata().total_num_calls.clone()
+            prev_h = prev_c = 0
+            for nb in range(NB + 1):
+                rt.get_config().num_bounces.fill_(nb)
+                rt.get_metadata().total_num_calls.copy_(calls0)
+                rt.raytrace()
+                h_, c_ = int(st.num_hits_per_pixel.sum().item()), int(st.num_composited_per_pixel.sum().item())
+                hh.append(h_ - prev_h), cc.append(c_ - prev_c)
+                prev_h, prev_c = h_, c_
+            rt.get_config().num_bounces.fill_(NB)
         # the launches that overlap inside the timed region (bounce forward, backward) are also timed one by one in a
         # short serial pass (one call per launch: no overlap), so that every kernel has a stand-alone duration
         serial = {}
-        ser_phases = [("trace_step1", _capi.EGR_PHASE_STEP(1))] if S > 1 else []
-        ser_phases += [(f"trace_step{s}", _capi.EGR_PHASE_STEP(s)) for s in range(2, S)] + [("backward", _capi.EGR_PHASE_FINISH)]
-        for i in range(3):
-            set_view_device(views_dev[my_views[Wm + i % K]])
-            with torch.enable_grad():
-                rt.update_bvh()
-                rt.raytrace_phases(_capi.EGR_PHASE_BEGIN | _capi.EGR_PHASE_STEP(0))
-                for name, mask in ser_phases:
-                    a, b = new_pair()
-                    a.record()
-                    rt.raytrace_phases(mask)
-                    b.record()
-                    serial.setdefault(name, []).append((a, b))
-        torch.cuda.synchronize()
-        rtr.zero_grad()
-        serial_ms = {k: sum(a.elapsed_time(b) for a, b in v) / len(v) for k, v in serial.items()}
-        alg = {"trace_step0": 44 * h0 + 40 * c0, "trace_step1": 44 * h1 + 40 * c1,
-               "backward": 260 * c0 + 176 * c1 + 56 * P}
-        kernel_ms = dict(serial_ms)
-        kernel_ms["trace_step0"] = phase_ms["trace_step0"]  # serial inside the timed region: measured there
+        kernel_ms = {}
+        if GRADS:
+            ser_phases = [(f"trace_step{s}", _capi.EGR_PHASE_STEP(s)) for s in range(1, S)] + [("backward", _capi.EGR_PHASE_FINISH)]
+            for i in range(3):
+                set_view_device(views_dev[my_views[Wm + i % K]])
+                with torch.enable_grad():
+                    rt.update_bvh()
+                    rt.raytrace_phases(_capi.EGR_PHASE_BEGIN | _capi.EGR_PHASE_STEP(0))
+                    for name, mask in ser_phases:
+                        a, b = new_pair()
+                        a.record()
+                        rt.raytrace_phases(mask)
+                        b.record()
+                        serial.setdefault(name, []).append((a, b))
+            torch.cuda.synchronize()
+            rtr.zero_grad()
+            kernel_ms = {k: sum(a.elapsed_time(b) for a, b in v) / len(v) for k, v in serial.items()}
+            kernel_ms["trace_step0"] = phase_ms["trace_step0"]  # serial inside the timed region: measured there
+        else:
+            kernel_ms = {f"trace_step{s}": phase_ms[f"trace_step{s}"] for s in range(NB + 1)}
+        serial_ms = {k: v for k, v in kernel_ms.items() if k != "trace_step0" or not GRADS}
+        alg = {f"trace_step{s}": 44 * hh[s] + 40 * cc[s] for s in range(NB + 1)}
+        if GRADS:
+            alg["backward"] = 260 * cc[0] + 176 * sum(cc[1:]) + 56 * P
         dom = max(alg, key=lambda k: kernel_ms.get(k, 0.0))
         achieved = alg[dom] / (kernel_ms[dom] * 1e-3) / 1e9
-        traffic = None
+        # ncu dram__bytes_read+write of the same kernels (profiles/traffic.json, written from the round's ncu capture);
+        # reported only while the library is not newer than that capture
+        traffic, traffic_note = None, None
         tpath = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(tpath):
+        if os.path.exists(tpath) and args.config == "c2":
             try:
-                traffic = json.load(open(tpath)).get(dom)
+                tj = json.load(open(tpath))
+                traffic = tj.get(dom)
+                if os.path.getmtime(_capi.lib_path()) > os.path.getmtime(tpath) + 1:
+                    traffic_note = "profiles/traffic.json is older than the library: capture predates the last kernel change"
             except Exception:
                 traffic = None
-        roofline = {"bound": "hbm", "kernel": {"trace_step0": "k_trace_step(step=0)", "trace_step1": "k_trace_step(step=1)",
-                                               "backward": "k_backward"}[dom],
+        kname = {f"trace_step{s}": f"k_trace_step(step={s})" for s in range(S)}
+        kname["backward"] = "k_backward"
+        roofline = {"bound": "hbm", "kernel": kname[dom],
                     "achieved": achieved, "peak": peak_gbs, "unit": "GB/s", "frac": achieved / peak_gbs,
-                    "traffic": traffic, "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
+                    "traffic": traffic, "traffic_note": traffic_note,
+                    "peak_source": peak_kind + " (MEASURED_PEAKS.json hbm_gbs)",
                     "algorithmic_bytes_per_launch": alg[dom], "avg_launch_ms": kernel_ms[dom],
-                    "timed_where": "timed region" if dom == "trace_step0" else "serial pass after the timed region",
+                    "timed_where": "timed region" if (dom == "trace_step0" or not GRADS) else "serial pass after the timed region",
                     "phase_ms": {k: round(v, 4) for k, v in phase_ms.items()},
                     "serial_kernel_ms": {k: round(v, 4) for k, v in serial_ms.items()},
-                    "hits_per_ray": {"accepted_step0": h0 / P, "composited_step0": c0 / P,
-                                     "accepted_step1": h1 / P, "composited_step1": c1 / P}}
+                    "frac_per_kernel": {k: round(alg[k] / (kernel_ms[k] * 1e-3) / 1e9 / peak_gbs, 4) for k in alg if kernel_ms.get(k)},
+                    "hits_per_ray": dict([(f"accepted_step{s}", hh[s] / P) for s in range(NB + 1)] +
+                                         [(f"composited_step{s}", cc[s] / P) for s in range(NB + 1)])}
 
     # ---------------- end to end through the renderer facade with HOST buffers (`e2e`) ----------------
     views_host = [scenes.SyntheticCamera(cams[i], targets[i % n_tg], device="cpu", pin=True) for i in range(n_tg)]
     for v in views_host:
         v.camera_center = v.camera_center.pin_memory()
-    h2d = sum(getattr(views_host[0], a).numel() * 4 for a in ("diffuse_image", "specular_image", "depth_image",
-                                                              "normal_image", "f0_image", "roughness_image")) + 12 + 36
+    h2d = 12 + 36
+    if GRADS:
+        h2d += sum(getattr(views_host[0], a).numel() * 4 for _, a in tkeys)
     out_host = torch.zeros(2, dtype=torch.float64).pin_memory()
     d2h = out_host.numel() * 8
 
     def e2e_step(i):
         v = views_host[i % n_tg]
-        with torch.enable_grad():
-            egr_b200.render(v, rtr, denoise=False)  # host->device copies of pose + 6 target images happen inside
-        if world > 1:
+        with grad_ctx():
+            egr_b200.render(v, rtr, denoise=False, targets_available=GRADS)  # host->device copies of pose (+ 6 target images) happen inside
+        if world > 1 and GRADS:
             distributed.allreduce_gradients(g.grad_records)
-        res = torch.stack([rt.get_stats().num_steps_per_pixel.sum().double(), pc._xyz.grad.abs().sum().double()])
+        probe = pc._xyz.grad.abs().sum().double() if GRADS else fb.output_final.sum().double()
+        res = torch.stack([rt.get_stats().num_steps_per_pixel.sum().double(), probe])
         out_host.copy_(res, non_blocking=False)  # device->host read of the step's result
         return float(out_host[0])
 
@@ -372,23 +424,77 @@ def run_ours(args):
            "d2h_bytes_per_step": int(d2h), "ms_per_step": e_ms / K,
            "api": "egr_b200.render(view, GaussianRaytracer) == reference renderer.render (export, refit, trace, import)"}
 
+    # ---------------- train iterations per second (the second half of BASELINE.json's `metric`) ----------------
+    # One iteration = train.py:211-254: render() with the pose and the six target images in pinned HOST memory ->
+    # all-reduce of the gradient record (world > 1) -> the fused optimiser step (gradient import + scale decay + Adam
+    # + clamps + zeroing).  Each step's parameters feed the next export.  The prune -> compact -> rebind -> resize ->
+    # export -> rebuild pipeline of every `pruning_interval`-th iteration is timed once and amortised.
+    train = None
+    if GRADS and not args.no_train:
+        from egr_b200 import trainer as trainer_mod
+
+        rtr.zero_grad()
+        tr = trainer_mod.Trainer(pc, rtr, pruning_interval=10 ** 9)  # the prune is timed separately below
+        tviews = [views_host[(i * world + rank) % n_tg] for i in range(Wm + K)]  # a different view on every rank
+        for i in range(max(Wm, 3)):
+            tr.step(tviews[i % len(tviews)])
+        sync()
+        tnames = ["render", "allreduce", "optimizer"]
+        tev = [{n: new_pair() for n in tnames} for _ in range(K)]
+        a, b = new_pair()
+        a.record()
+        for i in range(K):
+            tr.step(tviews[i], tev[i])
+        b.record()
+        sync()
+        it_ms = distributed.max_over_ranks(a.elapsed_time(b), dev) / K
+        tphase = {n: sum(e[n][0].elapsed_time(e[n][1]) for e in tev) / K for n in tnames}
+        # pruning interval: threshold = the 10th percentile of the accumulated weights (same on all ranks: the weights
+        # are all-reduced), so that ~10 % of the Gaussians go
+        tw = tr.total_weight.reshape(-1)
+        thr = float(torch.quantile(tw[:: max(1, tw.numel() // 1_000_000)].float(), 0.10).item())
+        keep = (tw > thr).to(torch.uint8)
+        n_before = int(tw.numel())
+        sync()
+        a, b = new_pair()
+        a.record()
+        n_after = tr.prune(keep)
+        b.record()
+        sync()
+        prune_ms = distributed.max_over_ranks(a.elapsed_time(b), dev)
+        for i in range(2):  # the model still trains after the prune (rebound optimiser state, rebuilt BVH)
+            tr.step(tviews[i])
+        sync()
+        interval = 125  # config.py:75 pruning_interval
+        amort = it_ms + prune_ms / interval
+        train = {"iter_per_s": 1e3 / amort, "views_per_s": world * 1e3 / amort, "ms_per_iter": it_ms,
+                 "phase_ms": {k: round(v, 4) for k, v in tphase.items()},
+                 "prune_rebuild_ms": prune_ms, "pruned": [n_before, n_after], "pruning_interval": interval,
+                 "iter_per_s_without_prune": 1e3 / it_ms,
+                 "what": "render(host targets) + all-reduce + fused Adam step per iteration; prune+compact+rebind+"
+                         "resize+export+rebuild timed once and amortised over the pruning interval",
+                 "finite": bool(torch.isfinite(pc._xyz).all().item())}
+
     if rank == 0:
         cpu = None
-        if world == 1 and not args.no_cpu:
+        if world == 1 and not args.no_cpu and args.config == "c2":
             cpu = cpu_sample("reference", scene, cams[0], args.cpu_pixels)
             cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
-        overflow = int(rt.get_stats().hitlog_status[2].item())
+        overflow = int(rt.hitlog_overflowed())
+        # grads: refit, pack+begin, S forward launches, S-1 scans, S backward launches, end; forward only: pack+begin,
+        # NB+1 forward launches, NB scans, resolve, end
+        n_launch = (1 + 2 + S + (S - 1) + S + 1) if GRADS else (2 + (NB + 1) + NB + 1 + 1)
         line = {
-            "metric": METRIC, "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
+            "metric": cf["metric"], "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "num_gaussians": N, "resolution": [R, R], "views": len(cams),
+            "config": {"workload": cf["workload"], "num_gaussians": N, "resolution": [Wd, Hd], "views": len(cams),
                        "views_per_step": world, "sharding": "views sharded over ranks, scene+BVH replicated, one "
                        "all-reduce of the flat [N,24] gradient record" if world > 1 else "single GPU",
                        "l2": "inputs larger than L2: >400 MB of records/nodes/params/state/hit log touched per step, "
                              "a different view every step", "hitlog_overflow": overflow},
-            "clocks": clocks, "e2e": e2e, "gpu_launches": (1 + 2 + S + (S - 1) + S + 1) * K,  # refit, pack+begin, S steps, S-1 scans, S backward, end
-            "roofline": roofline, "cpu_baseline": cpu, "rays_per_step": rays / K / world,
+            "clocks": clocks, "e2e": e2e, "gpu_launches": n_launch * K,
+            "roofline": roofline, "cpu_baseline": cpu, "rays_per_step": rays / K / world, "train": train,
         }
         print(json.dumps(line))
     if world > 1:
@@ -401,8 +507,10 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--num-gaussians", type=int, default=1_000_000)
-    ap.add_argument("--res", type=int, default=800)
+    ap.add_argument("--config", default="c2", choices=sorted(CONFIGS), help="named shape of BASELINE.json (default: the metric's C2)")
+    ap.add_argument("--num-gaussians", type=int, default=0, help="override the config's Gaussian count")
+    ap.add_argument("--res", type=int, default=0, help="override the config's resolution (square)")
+    ap.add_argument("--no-train", action="store_true", help="skip the train-iteration leg")
     ap.add_argument("--hitlog-hits", type=int, default=120_000_000)
     ap.add_argument("--cpu-pixels", type=int, default=2048)
     ap.add_argument("--no-cpu", action="store_true")

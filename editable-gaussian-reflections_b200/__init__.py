@@ -12,6 +12,7 @@ from .knn import distCUDA2  # noqa: F401
 from . import prune  # noqa: F401
 from . import edit  # noqa: F401
 from . import optim  # noqa: F401
+from . import trainer  # noqa: F401
 
 
 def make_raytracer(image_width: int, image_height: int, num_gaussians: int, ppll_forward_size: int = 180_000_000,
@@ -21,4 +22,4 @@ def make_raytracer(image_width: int, image_height: int, num_gaussians: int, ppll
 
 
 __all__ = ["make_raytracer", "Raytracer", "GaussianRaytracer", "render", "scenes", "distributed", "build", "_capi",
-           "DEFAULT_MAX_BOUNCES", "distCUDA2", "prune", "edit", "optim"]
+           "DEFAULT_MAX_BOUNCES", "distCUDA2", "prune", "edit", "optim", "trainer"]

@@ -208,6 +208,15 @@ class Raytracer:
                  backward_ppll_size=120_000_000, max_bounces=None, debug_rays=False):
         self._lib = _capi.load()
         dev = _dev()
+        self._make_holders(dev, image_width, image_height, num_gaussians, forward_ppll_size, backward_ppll_size,
+                           max_bounces, debug_rays)
+        self._pixel_state = torch.empty(self._lib.egr_pixel_state_bytes(self.width, self.height, self._S),
+                                        dtype=torch.uint8, device=dev)
+        self.rebuild_bvh()  # raytracer.cpp:70-71 (BVHWrapper ctor builds the TLAS)
+
+    def _make_holders(self, dev, image_width, image_height, num_gaussians, forward_ppll_size, backward_ppll_size,
+                      max_bounces, debug_rays):
+        """The tensor holders of raytracer.cpp:45-68 (everything the callers read or mutate in place)."""
         self._dev = dev
         self.width, self.height = int(image_width), int(image_height)
         self._max_bounces = DEFAULT_MAX_BOUNCES if max_bounces is None else int(max_bounces)
@@ -227,12 +236,10 @@ class Raytracer:
             self.gaussian_data.resize(int(num_gaussians))
         self._hitlog_capacity_hits = int(backward_ppll_size)
         self._hitlog = None
-        self._pixel_state = torch.empty(self._lib.egr_pixel_state_bytes(self.width, self.height, S),
-                                        dtype=torch.uint8, device=dev)
         self._bvh_storage = None
         self._bvh_count = -1
         self._params = None
-        self.rebuild_bvh()  # raytracer.cpp:70-71 (BVHWrapper ctor builds the TLAS)
+        self._ray_override = None
 
     # ---- constants (raytracer.cpp:145-148) -------------------------------------------------------------
     def MAX_BOUNCES(self=None):

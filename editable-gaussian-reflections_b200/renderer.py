@@ -34,6 +34,9 @@ class GaussianRaytracer:
         config.exp_power.fill_(pc.cfg.exp_power)
         self.pc = pc
         self._upload_stream = None
+        # False when the optimiser reads the tracer's gradient record directly (optim.FusedAdam / trainer.Trainer):
+        # the eight `.grad.add_` of _import_param_gradients are then skipped
+        self.import_gradients = True
         self._export_param_values()
         self.cuda_module.rebuild_bvh()
 
@@ -150,7 +153,7 @@ class GaussianRaytracer:
             self.cuda_module.raytrace()
         if denoise:
             self.cuda_module.denoise()
-        if torch.is_grad_enabled():
+        if torch.is_grad_enabled() and self.import_gradients:
             self._import_param_gradients()
         return {"render": fb.output_rgb.clone()}
 
