@@ -110,6 +110,8 @@ SYMBOLS = {
     "egr_compact_scratch_bytes": (C.c_size_t, [C.c_uint32]),
     "egr_compact_rows": (C.c_int, [_FP, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
                                    C.POINTER(C.c_uint32), _FP, C.c_size_t, _FP, _FP]),
+    "egr_duplicate_rows": (C.c_int, [_FP, C.c_uint32, C.c_uint32, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                     C.POINTER(C.c_uint32), C.c_int, C.POINTER(C.c_float), _FP, C.c_size_t, _FP, _FP]),
     "egr_select_box": (C.c_int, [_FP, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_float), _FP, _FP]),
     "egr_select_cylinder": (C.c_int, [_FP, C.c_uint32, C.POINTER(C.c_float), C.POINTER(C.c_float), _FP, _FP]),
     "egr_edit_apply": (C.c_int, [_FP, C.c_uint32, _FP, _FP, _FP, _FP, C.POINTER(EgrEdit), _FP]),
@@ -119,6 +121,7 @@ SYMBOLS = {
     "egr_raytrace_phases": (C.c_int, [C.POINTER(EgrParams), C.c_int, C.c_uint32, _FP]),
     "egr_reset_accumulators": (C.c_int, [C.POINTER(EgrParams), _FP]),
     "egr_denoise_passthrough": (C.c_int, [C.POINTER(EgrParams), _FP]),
+    "egr_denoise": (C.c_int, [C.POINTER(EgrParams), _FP]),
     "egr_hitlog_export": (C.c_int, [C.POINTER(EgrParams), C.c_int, C.c_int, _FP, _FP, _FP, _FP]),
     "egr_bvh_export": (C.c_int, [_FP, C.c_size_t, C.c_uint32, _FP, _FP, _FP, _FP, _FP]),
 }

@@ -16,7 +16,7 @@ CSRC = os.path.join(HERE, "csrc")
 # sources with other -D switches, see tools/build_variant.py); it is never rebuilt automatically.
 _LIB_OVERRIDE = os.environ.get("EGR_B200_LIB")
 LIB_PATH = _LIB_OVERRIDE or os.path.join(CSRC, "libegr_b200.so")
-SOURCES = ["egr_capi.cu", "egr_bvh.cu", "egr_trace.cu", "egr_backward.cu", "egr_prune.cu", "egr_edit.cu"]
+SOURCES = ["egr_capi.cu", "egr_bvh.cu", "egr_trace.cu", "egr_backward.cu", "egr_prune.cu", "egr_edit.cu", "egr_denoise.cu"]
 HEADERS = ["egr_common.cuh", "egr_trace.cuh", os.path.join("..", "..", "include", "egr_b200.h"),
            os.path.join("..", "..", "include", "egr_detmath.h")]
 NVCC_FLAGS = [

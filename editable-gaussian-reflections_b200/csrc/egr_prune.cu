@@ -77,6 +77,33 @@ k_compact(const uint8_t *__restrict__ keep, const uint32_t *__restrict__ pos, ui
     }
 }
 
+// Duplicate (row f2, EditableGaussianModel.duplicate_object): dst = cat(src, src[mask] (+ add)), one launch for all
+// arrays.  One thread per source word: copies it to the same place, and, when its row is selected, also to row
+// n + pos[row] (pos = exclusive scan of the mask); `add` (one designated float array, e.g. the means) is added to the
+// appended copy only.
+struct DupAdd {
+    int array;      // index of the array that receives the offset, or -1
+    float row[16];
+};
+__global__ void __launch_bounds__(256)
+k_duplicate(const uint8_t *__restrict__ mask, const uint32_t *__restrict__ pos, uint32_t n, CompactArrays a, DupAdd add) {
+    const uint32_t w = a.words[blockIdx.y];
+    const uint32_t *__restrict__ src = a.src[blockIdx.y];
+    uint32_t *__restrict__ dst = a.dst[blockIdx.y];
+    const bool offset = add.array == (int)blockIdx.y;
+    const uint32_t total = n * w;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const uint32_t row = i / w, k = i - row * w;
+        const uint32_t v = src[i];
+        dst[i] = v;
+        if (mask[row]) {
+            uint32_t o = v;
+            if (offset) o = __float_as_uint(__fadd_rn(__uint_as_float(v), add.row[k]));
+            dst[(size_t)(n + pos[row]) * w + k] = o;
+        }
+    }
+}
+
 __global__ void k_compact_count(const uint8_t *keep, const uint32_t *pos, uint32_t n, uint32_t *count_out) {
     if (threadIdx.x == 0 && blockIdx.x == 0) *count_out = pos[n - 1] + (keep[n - 1] ? 1u : 0u);
 }
@@ -164,6 +191,60 @@ extern "C" int egr_compact_rows(const uint8_t *keep, uint32_t n, uint32_t num_ar
         k_compact<<<dim3(bx, num_arrays), 256, 0, st>>>(keep, pos, n, a);
     }
     k_compact_count<<<1, 32, 0, st>>>(keep, pos, n, count_out);
+    EGR_CUDA_TRY(cudaGetLastError());
+    return EGR_OK;
+}
+
+extern "C" int egr_duplicate_rows(const uint8_t *mask, uint32_t n, uint32_t num_arrays, const void *const *src,
+                                  void *const *dst, const uint32_t *row_bytes, int add_array, const float *add_row,
+                                  void *scratch, size_t scratch_bytes, uint32_t *count_out, void *stream) {
+    if (!count_out) {
+        set_error("egr_duplicate_rows: count_out is null");
+        return EGR_EINVAL;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    if (n == 0) {
+        EGR_CUDA_TRY(cudaMemsetAsync(count_out, 0, 4, st));
+        return EGR_OK;
+    }
+    if (!mask || num_arrays > EGR_COMPACT_MAX_ARRAYS || (num_arrays && (!src || !dst || !row_bytes)) ||
+        add_array >= (int)num_arrays || (add_array >= 0 && !add_row)) {
+        set_error("egr_duplicate_rows: bad arguments (at most %d arrays)", EGR_COMPACT_MAX_ARRAYS);
+        return EGR_EINVAL;
+    }
+    if (!scratch || scratch_bytes < egr_compact_scratch_bytes(n) || ((uintptr_t)scratch & 255u)) {
+        set_error("egr_duplicate_rows: scratch too small or not 256-byte aligned (%zu needed)", egr_compact_scratch_bytes(n));
+        return EGR_ENOMEM;
+    }
+    if ((uint64_t)n * 2 * 16 > 0xffffffffull) {
+        set_error("egr_duplicate_rows: too many rows: %u", n);
+        return EGR_EINVAL;
+    }
+    CompactArrays a;
+    DupAdd add;
+    add.array = add_array;
+    for (int k = 0; k < 16; ++k) add.row[k] = 0.0f;
+    for (uint32_t k = 0; k < num_arrays; ++k) {
+        if (!src[k] || !dst[k] || src[k] == dst[k] || row_bytes[k] == 0 || row_bytes[k] % 4 || row_bytes[k] > 64 ||
+            ((uintptr_t)src[k] & 3u) || ((uintptr_t)dst[k] & 3u)) {
+            set_error("egr_duplicate_rows: array %u: null / aliased / misaligned pointer or row size %u not in {4..64 step 4}",
+                      k, row_bytes[k]);
+            return EGR_EINVAL;
+        }
+        a.src[k] = (const uint32_t *)src[k], a.dst[k] = (uint32_t *)dst[k], a.words[k] = row_bytes[k] / 4;
+    }
+    if (add_array >= 0)
+        for (uint32_t k = 0; k < row_bytes[add_array] / 4; ++k) add.row[k] = add_row[k];
+    uint32_t *pos = (uint32_t *)scratch;
+    void *temp = (char *)scratch + align_up((size_t)n * 4, 256);
+    size_t temp_bytes = scan_temp_bytes(n);
+    cub::TransformInputIterator<uint32_t, KeepToU32, const uint8_t *> it(mask, KeepToU32());
+    EGR_CUDA_TRY(cub::DeviceScan::ExclusiveSum(temp, temp_bytes, it, pos, (int)n, st));
+    if (num_arrays) {
+        const uint32_t bx = (uint32_t)min((size_t)148 * 16, ((size_t)n * 16 + 255) / 256);
+        k_duplicate<<<dim3(bx, num_arrays), 256, 0, st>>>(mask, pos, n, a, add);
+    }
+    k_compact_count<<<1, 32, 0, st>>>(mask, pos, n, count_out);
     EGR_CUDA_TRY(cudaGetLastError());
     return EGR_OK;
 }

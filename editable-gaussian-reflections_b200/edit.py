@@ -86,3 +86,45 @@ def apply_edit(mask: torch.Tensor, *, mean=None, scale=None, rotation=None, opac
     with torch.cuda.device(mask.device), torch.no_grad():
         _capi.check(_capi.load().egr_edit_apply(m8.data_ptr(), n, *ptrs, C.byref(e),
                                                 torch.cuda.current_stream().cuda_stream))
+
+
+def duplicate(tensors, mask: torch.Tensor, add_index: int = -1, add_row=None):
+    """``[torch.cat((t, t[mask])) for t in tensors]`` with ``add_row`` added to the appended copy of
+    ``tensors[add_index]`` -- ``EditableGaussianModel.duplicate_object`` (editable_gaussian_model.py:284-322: the
+    means get ``offset + delta_xyz``) -- as one scan + one launch for all arrays and one host read (the number of
+    selected rows, needed to size the results).  Returns (list of new tensors, number of appended rows)."""
+    tensors = list(tensors)
+    if not mask.is_cuda or any(not t.is_cuda for t in tensors):
+        raise RuntimeError("duplicate expects CUDA tensors (there is no CPU fallback)")
+    n = int(mask.numel())
+    m8 = mask.reshape(-1)
+    m8 = (m8.view(torch.uint8) if m8.dtype == torch.bool else m8.to(torch.uint8)).contiguous()
+    extra = int(m8.count_nonzero().item())  # the one host read
+    srcs, dsts, rows = [], [], []
+    for t in tensors:
+        if t.shape[0] != n:
+            raise RuntimeError("every tensor must have mask.numel() rows")
+        s_ = t.detach().contiguous()
+        srcs.append(s_)
+        dsts.append(torch.empty((n + extra,) + tuple(s_.shape[1:]), dtype=s_.dtype, device=s_.device))
+        rows.append(s_[0].numel() * s_.element_size() if n else 4)
+    lib = _capi.load()
+    k = len(tensors)
+    src_p = (C.c_void_p * max(k, 1))(*[s_.data_ptr() for s_ in srcs])
+    dst_p = (C.c_void_p * max(k, 1))(*[d.data_ptr() for d in dsts])
+    row_b = (C.c_uint32 * max(k, 1))(*rows)
+    add = None
+    if add_index >= 0:
+        if tensors[add_index].dtype != torch.float32:
+            raise RuntimeError("the offset row applies to a float32 array")
+        vals = [float(v) for v in add_row]
+        if len(vals) * 4 != rows[add_index]:
+            raise RuntimeError("add_row must have one value per column of tensors[add_index]")
+        add = (C.c_float * len(vals))(*vals)
+    count = torch.zeros(1, dtype=torch.int32, device=mask.device)
+    with torch.cuda.device(mask.device), torch.no_grad():
+        scratch = torch.empty(int(lib.egr_compact_scratch_bytes(n)) + 256, dtype=torch.uint8, device=mask.device)
+        _capi.check(lib.egr_duplicate_rows(m8.data_ptr(), n, k, src_p, dst_p, row_b, int(add_index), add,
+                                           scratch.data_ptr(), scratch.numel(), count.data_ptr(),
+                                           torch.cuda.current_stream().cuda_stream))
+    return dsts, extra

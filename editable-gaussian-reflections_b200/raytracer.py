@@ -386,9 +386,13 @@ class Raytracer:
         self._ensure_hitlog(grads)
         _capi.check(self._lib.egr_raytrace_phases(C.byref(self._params), int(grads), int(phase_mask), self._stream()))
 
-    def denoise(self):
-        """OptiX AI denoiser is unavailable (proprietary driver network): documented pass-through."""
-        _capi.check(self._lib.egr_denoise_passthrough(C.byref(self._params), self._stream()))
+    def denoise(self, passthrough: bool = False):
+        """``output_final -> output_denoised``.  The reference runs the OptiX AI denoiser here, a proprietary network
+        inside the driver that is unavailable on this box; this is a headless stand-in, NOT that network: an
+        edge-avoiding a-trous wavelet filter guided by the primary-step normal and depth (``egr_denoise``,
+        include/egr_b200.h).  ``passthrough=True`` copies ``output_final`` unchanged instead."""
+        fn = self._lib.egr_denoise_passthrough if passthrough else self._lib.egr_denoise
+        _capi.check(fn(C.byref(self._params), self._stream()))
 
     def reset_accumulators(self):
         _capi.check(self._lib.egr_reset_accumulators(C.byref(self._params), self._stream()))

@@ -224,6 +224,20 @@ int egr_reset_accumulators(const EgrParams *p, void *stream);
 /* DenoiserWrapper::run (csrc/optix/denoiser_wrapper.h:76-104): the OptiX AI denoiser is a proprietary
  * driver-resident network, unavailable here; this is the documented pass-through output_final -> output_denoised. */
 int egr_denoise_passthrough(const EgrParams *p, void *stream);
+/* Headless stand-in for DenoiserWrapper::run, used by Raytracer.denoise(): an edge-avoiding a-trous wavelet filter
+ * (Dammertz et al. 2010) of output_final into output_denoised, guided by the primary-step normal (the guide layer the
+ * reference gives OptiX, denoiser_wrapper.h:88-96) and the primary-step depth.  EGR_DENOISE_PASSES passes of a 5x5
+ * B3-spline kernel with hole sizes 1, 2, 4 ...; tap weight = kernel * exp(-(|dc|^2/sigma_c^2 + |dn|^2/sigma_n^2 +
+ * (dd/(|d|+eps))^2/sigma_d^2)), sigma_c halved after every pass.  It is NOT the OptiX network (which is unavailable
+ * on this box); it keeps geometric edges and removes the Monte-Carlo noise of the sampled reflection directions.
+ * Scratch: six step-0 planes of pixel_state that are dead between two egr_raytrace calls (call it after the trace
+ * whose output it filters, and before egr_hitlog_export's of an earlier trace are no longer needed). */
+#define EGR_DENOISE_PASSES 3
+#define EGR_DENOISE_SIGMA_COLOR 0.6f
+#define EGR_DENOISE_SIGMA_NORMAL 0.3f
+#define EGR_DENOISE_SIGMA_DEPTH 0.05f
+#define EGR_DENOISE_DEPTH_EPS 1.0e-3f
+int egr_denoise(const EgrParams *p, void *stream);
 
 /* ---- next row f3: `distCUDA2` of the reference's simple-knn submodule
  *      (submodules/simple-knn/simple_knn.cu:46-222, spatial.cu; Python call sites scene/gaussian_model.py:197-200,
@@ -287,6 +301,16 @@ int egr_select_box(const float *mean, uint32_t n, const float *min3, const float
 int egr_select_cylinder(const float *mean, uint32_t n, const float *min3, const float *max3, uint8_t *mask, void *stream);
 int egr_edit_apply(const uint8_t *mask, uint32_t n, float *mean, float *scale, float *rotation, float *opacity,
                    const EgrEdit *edit, void *stream);
+/* egr_duplicate_rows: EditableGaussianModel.duplicate_object (scene/editable_gaussian_model.py:284-322: nine
+ *   `tensor[selection].clone()` + nine `torch.cat`, i.e. ~27 launches and a host sync per indexing) as one scan + ONE
+ *   launch: for every array a, dst[a] = cat(src[a], src[a][mask]); the appended copy of array `add_array` (the means;
+ *   -1 for none) additionally gets the HOST row `add_row` added (offset + edit translation, :290).  Same argument
+ *   conventions as egr_compact_rows; dst[a] must have room for n + (number of selected rows) rows -- the caller
+ *   learns that number from the mask (one host read, as the reference's indexing needs) or from an upper bound;
+ *   *count_out (device) receives it as well.  scratch: egr_compact_scratch_bytes(n), 256-aligned. */
+int egr_duplicate_rows(const uint8_t *mask, uint32_t n, uint32_t num_arrays, const void *const *src, void *const *dst,
+                       const uint32_t *row_bytes, int add_array, const float *add_row, void *scratch,
+                       size_t scratch_bytes, uint32_t *count_out, void *stream);
 
 /* ---- next row f1: the host step around the tracer as ONE launch.  Reference, per iteration:
  *      _import_param_gradients (renderer/gaussian_raytracer.py:53-62, 8 add_), the scale decay

@@ -4,10 +4,14 @@ Follows ``editable_gauss_refl/scene/editable_gaussian_model.py`` operation by op
 runs each op as its own kernel, so every intermediate is rounded to float32):
   select_box       :45-48      select_cylinder  :30-44
   edit_xyz         :201-238    edit_scaling     :240-254    edit_rotation :256-279    remove :324-328
-The reference module cannot be imported here (it needs ``kornia``, absent from this image, and a CUDA device), so
-the three kornia conversions it calls are restated from their published definitions (Rodrigues' formula,
-unit-quaternion <-> matrix): parity of those three is UNPINNED; tests compare rotations as matrices (a unit
-quaternion and its negative are the same rotation) within a stated tolerance.  The 3x3 product of edit_xyz is a GEMM
+Pinning: the reference module cannot be imported here (it needs ``kornia``, absent from this image, and a CUDA
+device).  Everything in it that is plain torch -- the masks, the translate / scale part of get_xyz, the scaling edit,
+remove_object and duplicate_object -- is pinned by running the reference's own torch expressions on the GPU next to
+the kernels (tests/test_edit.py::test_kernels_match_the_reference_torch_expressions_run_on_the_gpu, bit for bit).
+The three kornia conversions it calls are restated from their published definitions (Rodrigues' formula,
+unit-quaternion <-> matrix) and pinned to hand-computed known answers (quarter turns about each axis, a 120-degree
+turn about (1,1,1), the composition order R_edit @ R(q): test_rotation_conversions_known_answers); tests compare
+rotations as matrices (a unit quaternion and its negative are the same rotation) within a stated tolerance.  The 3x3 product of edit_xyz is a GEMM
 in the reference (summation order unspecified): compared within tolerance as well.  Everything else is bit-exact.
 """
 import numpy as np

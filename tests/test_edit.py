@@ -126,3 +126,99 @@ def test_edit_then_refit_renders_like_an_edited_upload():
         rt2.raytrace()
     b = H.gpu_outputs(rt2)["rgb"]
     assert float(np.abs(a - b).max()) <= 1e-4 and float(np.abs(a).max()) > 0
+
+
+@pytest.mark.gpu
+def test_kernels_match_the_reference_torch_expressions_run_on_the_gpu():
+    """Pins row f2 to the reference itself where its code can run here: the reference's OWN torch expressions for the
+    selection masks (editable_gaussian_model.py:30-48), the translate / scale part of ``get_xyz`` (:208-224), the
+    scaling edit (:242-253), ``remove_object`` (:324-328) and ``duplicate_object`` (:284-306) are executed on the
+    same GPU (they are plain torch, no kornia) and compared with the kernels bit for bit -- the way tests/test_optim.py
+    pins the fused optimiser step.  Only the three kornia rotation conversions cannot run (kornia is absent from the
+    image); those are pinned to hand-computed known answers in test_rotation_conversions_known_answers."""
+    import torch
+
+    from egr_b200 import edit
+
+    xyz, scale, rotq, opac = _cloud(seed=3)
+    dev = "cuda"
+    t_xyz, t_scale, t_opac = (torch.from_numpy(v).to(dev) for v in (xyz, scale, opac))
+    for lo, hi in BOXES:
+        # :45-48 (box) and :30-44 (elliptic cylinder), verbatim torch
+        min_bound, max_bound = torch.tensor(lo, device=dev), torch.tensor(hi, device=dev)
+        dist1, dist2 = t_xyz - min_bound, t_xyz - max_bound
+        ref_box = (dist1 >= 0).all(dim=-1) & (dist2 <= 0).all(dim=-1)
+        center_xy = 0.5 * (min_bound[[0, 1]] + max_bound[[0, 1]])
+        half_extent_xy = 0.5 * (max_bound[[0, 1]] - min_bound[[0, 1]])
+        normalized = (t_xyz[:, [0, 1]] - center_xy) / half_extent_xy
+        ref_cyl = ((normalized**2).sum(dim=-1) <= 1.0) & (t_xyz[:, 2] >= min_bound[2]) & (t_xyz[:, 2] <= max_bound[2])
+        assert torch.equal(edit.select_box(t_xyz, lo, hi).bool(), ref_box), (lo, hi)
+        assert torch.equal(edit.select_cylinder(t_xyz, lo, hi).bool(), ref_cyl), (lo, hi)
+    lo, hi = BOXES[1]
+    sel = edit.select_box(t_xyz, lo, hi).bool()
+    tr, sc = (0.25, -0.5, 0.125), 1.3
+    # get_xyz :208-224 (no rotation), verbatim torch
+    ref_xyz = t_xyz.clone()
+    ref_xyz[sel] += torch.tensor(tr, device=dev)
+    bbox_center = torch.tensor([(lo[i] + hi[i]) / 2 for i in range(3)], device=dev)
+    object_center = bbox_center + torch.tensor(tr, device=dev)
+    ref_xyz[sel] = (ref_xyz[sel] - object_center) * sc + object_center
+    # _get_scaling :242-253
+    scaling = torch.exp(t_scale)
+    scaling[sel] *= sc
+    ref_scale = torch.log(scaling)
+    # remove_object :324-328
+    ref_opac = t_opac.clone()
+    ref_opac[sel] *= 0.0
+    ref_opac[sel] -= 100000000.0
+    got = dict(mean=t_xyz.clone(), scale=t_scale.clone(), opacity=t_opac.clone())
+    edit.apply_edit(sel, mean=got["mean"], scale=got["scale"], translate=tr,
+                    center=[(lo[i] + hi[i]) / 2 for i in range(3)], scale_factor=sc)
+    edit.apply_edit(sel, opacity=got["opacity"], kill=True)
+    assert torch.equal(got["mean"], ref_xyz)
+    assert torch.equal(got["scale"][sel], ref_scale[sel])  # same exp / multiply / log, same device libm
+    assert torch.equal(got["scale"][~sel], t_scale[~sel])
+    assert torch.equal(got["opacity"], ref_opac)
+    # duplicate_object :284-306: clone the selection (+ offset + translation on the means), concatenate
+    offset, delta = 0.3, torch.tensor(tr, device=dev)
+    arrays = [t_xyz, torch.from_numpy(rotq).to(dev), t_scale, t_opac]
+    ref_new = [torch.cat((a, a[sel].clone() + offset + delta if i == 0 else a[sel].clone()), dim=0) for i, a in enumerate(arrays)]
+    add_row = (torch.tensor(offset) + torch.tensor(tr)).tolist()  # float32 `offset + delta_xyz`, then added to the rows
+    new, extra = edit.duplicate(arrays, sel, add_index=0, add_row=add_row)
+    assert extra == int(sel.sum()) and extra > 100
+    for a, b in zip(new[1:], ref_new[1:]):
+        assert torch.equal(a, b)
+    # the reference adds `offset` and `delta_xyz` one after the other; the kernel adds their float32 sum once
+    assert torch.equal(new[0][: t_xyz.shape[0]], t_xyz)
+    assert float((new[0] - ref_new[0]).abs().max()) <= 2.4e-7 * 4.0
+    none, zero = edit.duplicate(arrays, torch.zeros_like(sel))
+    assert zero == 0 and all(torch.equal(a, b) for a, b in zip(none, arrays))
+
+
+def test_rotation_conversions_known_answers():
+    """The kornia conversions the reference calls (axis-angle -> matrix, quaternion <-> matrix, :223-236, :256-279)
+    cannot be imported here; the restatements used by the product (edit.axis_angle_to_matrix_and_quaternion) and by
+    the oracle are pinned to hand-computed answers: quarter turns about each axis, the composition order
+    R_edit @ R(q), and a general axis."""
+    from egr_b200 import edit
+
+    ex, ey, ez = np.eye(3)
+    Rx, qx = edit.axis_angle_to_matrix_and_quaternion(90, 0, 0)
+    Ry, qy = edit.axis_angle_to_matrix_and_quaternion(0, 90, 0)
+    Rz, qz = edit.axis_angle_to_matrix_and_quaternion(0, 0, 90)
+    assert np.allclose(Rx @ ey, ez, atol=1e-6) and np.allclose(Rx @ ez, -ey, atol=1e-6) and np.allclose(Rx @ ex, ex, atol=1e-6)
+    assert np.allclose(Ry @ ez, ex, atol=1e-6) and np.allclose(Ry @ ex, -ez, atol=1e-6)
+    assert np.allclose(Rz @ ex, ey, atol=1e-6) and np.allclose(Rz @ ey, -ex, atol=1e-6)
+    h = np.sqrt(0.5)
+    assert np.allclose(qx, [h, h, 0, 0], atol=1e-6) and np.allclose(qy, [h, 0, h, 0], atol=1e-6) and np.allclose(qz, [h, 0, 0, h], atol=1e-6)
+    for R, q in ((Rx, qx), (Ry, qy), (Rz, qz)):
+        assert np.allclose(eo.quaternion_to_matrix(q), R, atol=1e-6) and np.allclose(eo.axis_angle_to_matrix((0, 0, 0)), np.eye(3))
+    # the axis-angle VECTOR (not Euler angles): 120 degrees about (1,1,1)/sqrt(3) permutes the axes x -> y -> z -> x
+    a = 120.0 / np.sqrt(3.0)
+    R, q = edit.axis_angle_to_matrix_and_quaternion(a, a, a)
+    assert np.allclose(R @ ex, ey, atol=1e-6) and np.allclose(R @ ey, ez, atol=1e-6) and np.allclose(R @ ez, ex, atol=1e-6)
+    assert np.allclose(q, [0.5, 0.5, 0.5, 0.5], atol=1e-6) and np.allclose(eo.axis_angle_to_matrix((a, a, a)), R, atol=1e-6)
+    # composition order of _get_rotation (:275): R_edit @ R(q) -- the edit is applied AFTER the Gaussian's own rotation
+    M = eo.edit_rotation_matrices(np.array([qz]), np.array([True]), (90, 0, 0))[0]
+    assert np.allclose(M, Rx.astype(np.float64) @ Rz.astype(np.float64), atol=1e-6)
+    assert np.allclose(M @ ex, ez, atol=1e-6)  # x -(Rz)-> y -(Rx)-> z
