@@ -148,6 +148,7 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
         float p_r = 0.0f, w_r = 0.0f, p_d = 0.0f, w_d = 0.0f;
 
         for (int b = nb - 1; b >= 0; --b) {
+            EGR_CHECK(chunk < c.hitlog_chunks);
             const char *base = (const char *)c.p.hitlog + (size_t)chunk * HITLOG_CHUNK_BYTES;
             const uint2 *entries = (const uint2 *)(base + 128);
             const uint32_t prev = *(const uint32_t *)base;
@@ -164,6 +165,7 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
                 uint32_t id = 0;
                 if (has) {
                     const uint32_t j = e.x;
+                    EGR_CHECK(j < c.bvh.n);
                     const float Tr = __uint_as_float(e.y);
                     float4 r0, r1, r2, r3;
                     ldg2(&c.bvh.records[4 * (size_t)j], r0, r1);
@@ -175,6 +177,7 @@ __global__ void __launch_bounds__(128, 4) k_backward(const TraceCtx c, const int
                     const float dist = h.t, alpha = h.alpha;
                     const float sf = r1.w, sigma = r2.w;
                     id = __float_as_uint(r3.w);
+                    EGR_CHECK(id < gs.count);
                     const float gv = h.gaussval;
                     const float4 a0 = __ldg(&c.bvh.appearance[3 * (size_t)j + 0]);
                     const f3 c_rgb = mk3(a0.x, a0.y, a0.z);

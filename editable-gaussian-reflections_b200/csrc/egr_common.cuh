@@ -31,6 +31,16 @@ struct NvtxRange {
     NvtxRange &operator=(const NvtxRange &) = delete;
 };
 
+// Index checks of the debug variant (tools/build_variant.py <out.so> -DEGR_DEBUG_CHECKS): device-side asserts on every
+// index that addresses the tree, the records, the hit lists, the hit log and the gradient record.  compute-sanitizer is
+// closed on this pool, so the GPU test-suite is run once per round against that variant instead (profiles/).
+#ifdef EGR_DEBUG_CHECKS
+#include <assert.h>
+#define EGR_CHECK(c) assert(c)
+#else
+#define EGR_CHECK(c) ((void)0)
+#endif
+
 // ---- constants of the reference's flags.h ---------------------------------------------------------------
 constexpr float A_MAX = 0.9999f;            // flags.h:8  MAX_ALPHA
 constexpr int KBUF = 16;                    // flags.h:16 BUFFER_SIZE

@@ -63,6 +63,7 @@ __device__ __forceinline__ void list_bind(LaneList &L, char *region) {
 }
 __device__ __forceinline__ void list_reset(LaneList &L) { L.cnt = 0, L.maxt = -FLT_MAX, L.maxslot = 0; }
 __device__ __forceinline__ void list_add(LaneList &L, const uint32_t lane, const float t, const uint32_t leaf, const float alpha) {
+    EGR_CHECK(lane < 32 && L.maxslot < LIST_CAP);
     if (L.cnt < LIST_CAP) {
         L.t[L.cnt * 32 + lane] = t;
         L.la[L.cnt * 32 + lane] = make_uint2(leaf, __float_as_uint(alpha));
@@ -100,6 +101,7 @@ __device__ __forceinline__ void full_test(
     const BvhView &bvh, const StepCfg &sc, const float4 *rp, const uint32_t leaf, const f3 o, const f3 d,
     const float w, LaneList &L, float &T_full, int &n_acc, int &n_trav) {
     float4 r0, r1, r2, r3;
+    EGR_CHECK(leaf < bvh.n);
     if (SHARED) r0 = rp[0], r1 = rp[1], r2 = rp[2], r3 = rp[3];
     else ldg2(rp, r0, r1), ldg2(rp + 2, r2, r3);  // two 256-bit gathers (r0 was seen by the sphere test: an L1 hit)
     n_trav++;
@@ -167,6 +169,7 @@ __device__ __forceinline__ void traverse(
             continue;
         }
         const uint32_t first = tag & ~FIRST_LEAF_FLAG;
+        EGR_CHECK(nl >= 1 && nl <= FAT && first + nl <= bvh.n && skip > node && skip <= end);
         __syncwarp();
         for (uint32_t q = lane; q < nl * 4; q += 32) s_rec[q] = __ldg(&bvh.records[4 * (size_t)first + q]);
         __syncwarp();
@@ -258,6 +261,7 @@ __device__ __forceinline__ void traverse_lane(
                 continue;
             }
             // small subtree: its Gaussians are a contiguous record range, tested directly instead of descending
+            EGR_CHECK(nl >= 1 && (tag & ~FIRST_LEAF_FLAG) + nl <= bvh.n && skip > node && skip <= end);
             node = skip;
             if (leaf == NO_LEAF) {
                 leaf = tag & ~FIRST_LEAF_FLAG, leaf_n = nl;
@@ -416,6 +420,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
             const uint32_t bit = __ffs(m) - 1;
             if (step == 1) lane_pixel(c, 0, lo, bit, pix);
             else pix = c.ray_pix[(size_t)(step - 1) * c.P + lo * 32 + bit];
+            EGR_CHECK(pix < c.P && r < c.P);
             c.ray_pix[(size_t)step * c.P + r] = pix;
             o = plane3(c, SP_NEXT_O, step - 1, pix);
             d = plane3(c, SP_NEXT_D, step - 1, pix);
@@ -520,6 +525,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
                 log_ok = false;
             } else {
                 char *base = hitlog + (size_t)cidx * HITLOG_CHUNK_BYTES;
+                EGR_CHECK((size_t)(cidx + 1) * HITLOG_CHUNK_BYTES <= c.p.hitlog_bytes);
                 if (lane == 0) *(uint32_t *)base = tail_chunk;
                 chunk = (uint2 *)(base + 128);
                 tail_chunk = cidx;
@@ -546,6 +552,7 @@ __device__ __forceinline__ void trace_warp(const TraceCtx &c, const int step, co
                 w = fmaxf(w, t);  // forward_pass.cu:89
                 if (t < sc.tmax) {
                     const uint32_t j = kq.y;
+                    EGR_CHECK(j < c.bvh.n);
                     const float alpha = __uint_as_float(kq.z);  // as evaluated by the walk
                     const float4 a0 = __ldg(&c.bvh.appearance[3 * (size_t)j + 0]);
                     const float4 a1 = __ldg(&c.bvh.appearance[3 * (size_t)j + 1]);
