@@ -124,6 +124,8 @@ SYMBOLS = {
     "egr_denoise": (C.c_int, [C.POINTER(EgrParams), _FP]),
     "egr_hitlog_export": (C.c_int, [C.POINTER(EgrParams), C.c_int, C.c_int, _FP, _FP, _FP, _FP]),
     "egr_bvh_export": (C.c_int, [_FP, C.c_size_t, C.c_uint32, _FP, _FP, _FP, _FP, _FP]),
+    "egr_bvh_export_wide": (C.c_int, [_FP, C.c_size_t, C.c_uint32, _FP, _FP, _FP, _FP]),
+    "egr_bvh_wide_capacity": (C.c_uint32, [C.c_uint32]),
 }
 
 _lib = None
@@ -149,7 +151,12 @@ def load(build_if_missing: bool = True):
                 raise RuntimeError(f"CUDA extension missing and cannot be built: {e}") from e
     lib = C.CDLL(path)
     for name, (res, args) in SYMBOLS.items():
-        fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
+        try:
+            fn = getattr(lib, name)  # AttributeError if the library does not export a declared symbol
+        except AttributeError:
+            if os.environ.get("EGR_B200_LIB"):  # an experiment's variant built from older sources
+                continue
+            raise
         fn.restype = res
         fn.argtypes = args
     if lib.egr_abi_version() != EGR_ABI_VERSION:

@@ -3,6 +3,7 @@
 // Replaces the reference's opaque OptiX instance acceleration structure
 // (editable_gauss_refl/cuda/csrc/optix/bvh_wrapper.h:24-157, bvh_wrapper.cu:9-70).
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #include <float.h>
 
@@ -31,9 +32,12 @@ static BuildScratch build_scratch_layout(uint32_t n) {
     L.parent_leaf = o, o = align_up(o + (size_t)n * 4, 256);
     L.first = o, o = align_up(o + (size_t)n * 4, 256);
     L.last = o, o = align_up(o + (size_t)n * 4, 256);
-    size_t cub = 0;
+    size_t cub = 0, scan = 0;
     cub::DeviceRadixSort::SortPairs(nullptr, cub, (const uint64_t *)nullptr, (uint64_t *)nullptr,
                                     (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)n, 0, 64);
+    // the wide-node numbering scans one flag per binary node; it runs after the sort and shares its temporary block
+    cub::DeviceScan::ExclusiveSum(nullptr, scan, (const uint32_t *)nullptr, (uint32_t *)nullptr, (int)(2 * n));
+    if (scan > cub) cub = scan;
     L.cub_bytes = cub;
     L.cub_temp = o, o = align_up(o + cub, 256);
     L.total = o;
@@ -158,7 +162,8 @@ k_karras(const uint64_t *__restrict__ keys, int n, uint32_t *child_l, uint32_t *
 __global__ void __launch_bounds__(256)
 k_preorder(int n, const uint32_t *__restrict__ child_l, const uint32_t *__restrict__ parent_int,
            const uint32_t *__restrict__ parent_leaf, const uint32_t *__restrict__ first,
-           const uint32_t *__restrict__ last, float4 *nodes, uint32_t *parents, uint32_t *leaf_node, uint32_t *flags) {
+           const uint32_t *__restrict__ last, float4 *nodes, uint32_t *parents, uint32_t *leaf_node, uint32_t *flags,
+           uint32_t *wide_mark, uint32_t *wide_slot) {
     int tid = blockIdx.x * blockDim.x + threadIdx.x;
     if (tid >= 2 * n - 1) return;
     bool is_leaf = tid >= n - 1;
@@ -169,7 +174,7 @@ k_preorder(int n, const uint32_t *__restrict__ child_l, const uint32_t *__restri
     uint32_t cur_code = (idx << 1) | (is_leaf ? 1u : 0u);
     uint32_t p = is_leaf ? (n > 1 ? parent_leaf[idx] : NO_PARENT) : parent_int[idx];
     uint32_t direct_parent = p;
-    uint32_t first_turn = 0;
+    uint32_t first_turn = 0, depth = 0;
     bool first_iter = true;
     while (p != NO_PARENT) {
         uint32_t t = child_l[p] == cur_code ? 1u : 0u;
@@ -177,6 +182,7 @@ k_preorder(int n, const uint32_t *__restrict__ child_l, const uint32_t *__restri
         turns += t;
         cur_code = p << 1;
         p = parent_int[p];
+        ++depth;
     }
     uint32_t pre = 2u * a + turns;
     uint32_t skip = pre + 2u * nl - 1u;
@@ -188,6 +194,66 @@ k_preorder(int n, const uint32_t *__restrict__ child_l, const uint32_t *__restri
     parents[pre] = ppre;
     flags[pre] = 0;
     if (is_leaf) leaf_node[idx] = pre;
+    // root of a 4-wide node: every second level of the subtrees that are not a candidate range by themselves
+    if (wide_mark) wide_mark[pre] = (!is_leaf && nl > WIDE_FAT && (depth & 1u) == 0) ? 1u : 0u;
+    if (wide_slot) wide_slot[pre] = WIDE_NONE;
+}
+
+// ---- 4-wide tree of the per-lane walk (layout: egr_common.cuh) ---------------------------------------------------------
+__device__ __forceinline__ uint32_t node_leaves(const float4 *__restrict__ nodes, uint32_t node) {
+    return (__float_as_uint(nodes[2 * (size_t)node].w) - node + 1) >> 1;
+}
+// One thread per binary node; a marked node b becomes wide node wide_index[b].  Its slots are the grandchildren of b
+// (or a child, when that child is already a candidate range), in leaf order; each slot is a range link or the wide
+// node of that grandchild (which is marked: two levels down, more than WIDE_FAT leaves).
+__global__ void __launch_bounds__(256)
+k_wide_topology(BvhView bvh, const uint32_t *__restrict__ mark, const uint32_t *__restrict__ wide_index) {
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b == 0) *bvh.num_wide = bvh.num_nodes ? wide_index[bvh.num_nodes - 1] + mark[bvh.num_nodes - 1] : 0u;
+    if (b >= bvh.num_nodes || !mark[b]) return;
+    const float4 *__restrict__ nodes = bvh.nodes;
+    const uint32_t w = wide_index[b];
+    uint32_t slot[4] = {WIDE_NONE, WIDE_NONE, WIDE_NONE, WIDE_NONE};
+    int ns = 0;
+    const uint32_t kids[2] = {b + 1, __float_as_uint(nodes[2 * (size_t)(b + 1)].w)};  // left child, its skip = right child
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const uint32_t c = kids[k];
+        if (node_leaves(nodes, c) <= WIDE_FAT) {
+            slot[ns++] = c;
+        } else {
+            slot[ns++] = c + 1;
+            slot[ns++] = __float_as_uint(nodes[2 * (size_t)(c + 1)].w);
+        }
+    }
+    float4 *wn = bvh.wide + 8 * (size_t)w;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        uint32_t link = WIDE_NONE;
+        const uint32_t e = slot[i];
+        if (e != WIDE_NONE) {
+            const uint32_t nl = node_leaves(nodes, e);
+            if (nl <= WIDE_FAT) {
+                const uint32_t tag = __float_as_uint(nodes[2 * (size_t)e + 1].w);
+                link = WIDE_RANGE | ((nl - 1) << WIDE_CNT_SHIFT) | (tag & ~FIRST_LEAF_FLAG);  // (a leaf's tag is its own index)
+            } else {
+                link = wide_index[e];
+            }
+        }
+        if (e != WIDE_NONE) bvh.wide_slot[e] = 4 * w + (uint32_t)i;  // the refit mirrors e's box into this slot
+        wn[2 * i] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(link));  // empty box until the refit
+        wn[2 * i + 1] = make_float4(-1.0f, -1.0f, -1.0f, 0.0f);
+    }
+}
+// The refit mirrors every box it finishes into the wide slot that stands for that binary node (same inflated boxes, so
+// the wide walk is exactly as conservative as the binary one); the link in the slot's first .w is kept.
+__device__ __forceinline__ void mirror_box_to_wide(const BvhView &bvh, uint32_t node, const float4 a, const float4 b) {
+    if (!bvh.wide_slot) return;
+    const uint32_t ws = bvh.wide_slot[node];
+    if (ws == WIDE_NONE) return;
+    float *q = reinterpret_cast<float *>(bvh.wide + 2 * (size_t)ws);
+    q[0] = a.x, q[1] = a.y, q[2] = a.z;  // q[3] = link
+    reinterpret_cast<float4 *>(q)[1] = make_float4(b.x, b.y, b.z, 0.0f);
 }
 
 // Bottom-up box propagation from a finished leaf: the second arrival at a node merges its children and continues
@@ -221,6 +287,7 @@ __device__ __forceinline__ void merge_boxes_upward(const BvhView &bvh, uint32_t 
         b.w = pb.w;  // keep the first-leaf tag
         __stcg(&bvh.nodes[2 * (size_t)p], a);
         __stcg(&bvh.nodes[2 * (size_t)p + 1], b);
+        mirror_box_to_wide(bvh, p, a, b);
         p = bvh.parents[p];
     }
 }
@@ -294,6 +361,7 @@ __global__ void __launch_bounds__(256) k_refit(BvhView bvh, EgrGaussians g, EgrC
     uint32_t skip = node + 1;
     bvh.nodes[2 * (size_t)node] = make_float4(bmin[0], bmin[1], bmin[2], __uint_as_float(skip));
     bvh.nodes[2 * (size_t)node + 1] = make_float4(bmax[0], bmax[1], bmax[2], __uint_as_float(j));
+    mirror_box_to_wide(bvh, node, make_float4(bmin[0], bmin[1], bmin[2], 0.0f), make_float4(bmax[0], bmax[1], bmax[2], 0.0f));
 
     merge_boxes_upward(bvh, node);
 }
@@ -382,8 +450,15 @@ static int build_topology(const float *points, uint32_t n, const BvhView &v, con
                                                  (int)n, 0, 64, st));
     if (n > 1) k_karras<<<(n - 1 + 255) / 256, 256, 0, st>>>(keys_out, (int)n, child_l, child_r, parent_int,
                                                             parent_leaf, first, last);
+    // the sort keys are dead from here on: their two blocks (8 B per point each) hold one mark / one index per node
+    uint32_t *wide_mark = v.wide_cap ? (uint32_t *)keys_in : nullptr, *wide_index = (uint32_t *)keys_out;
     k_preorder<<<(2 * n - 1 + 255) / 256, 256, 0, st>>>((int)n, child_l, parent_int, parent_leaf, first, last, v.nodes,
-                                                        v.parents, v.leaf_node, v.flags);
+                                                        v.parents, v.leaf_node, v.flags, wide_mark, v.wide_slot);
+    if (v.wide_cap) {
+        size_t scan_bytes = B.cub_bytes;
+        EGR_CUDA_TRY(cub::DeviceScan::ExclusiveSum(sb + B.cub_temp, scan_bytes, wide_mark, wide_index, (int)(2 * n - 1), st));
+        k_wide_topology<<<(2 * n - 1 + 255) / 256, 256, 0, st>>>(v, wide_mark, wide_index);
+    }
     EGR_CUDA_TRY(cudaGetLastError());
     return EGR_OK;
 }
@@ -394,8 +469,8 @@ extern "C" int egr_bvh_build(const EgrGaussians *g, const EgrConfig *cfg, void *
     if (rc) return rc;
     const uint32_t n = g->count;
     if (n == 0) return EGR_OK;
-    if (n > 0x3fffffffu) {
-        set_error("too many gaussians: %u", n);
+    if (n > WIDE_MAX_GAUSSIANS) {
+        set_error("too many gaussians: %u (limit %u)", n, WIDE_MAX_GAUSSIANS);
         return EGR_EINVAL;
     }
     BvhLayout L = bvh_layout(n);
@@ -432,6 +507,23 @@ extern "C" int egr_bvh_export(const void *storage, size_t storage_bytes, uint32_
     if (parents) EGR_CUDA_TRY(cudaMemcpyAsync(parents, v.parents, (size_t)L.num_nodes * 4, cudaMemcpyDeviceToDevice, st));
     return EGR_OK;
 }
+
+extern "C" int egr_bvh_export_wide(const void *storage, size_t storage_bytes, uint32_t n, float *wide,
+                                   uint32_t *wide_slot, uint32_t *num_wide, void *stream) {
+    if (n == 0) return EGR_OK;
+    BvhLayout L = bvh_layout(n);
+    if (!storage || storage_bytes < L.total) {
+        set_error("bvh storage too small");
+        return EGR_ENOMEM;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    BvhView v = bvh_view(const_cast<void *>(storage), n);
+    if (wide) EGR_CUDA_TRY(cudaMemcpyAsync(wide, v.wide, (size_t)L.wide_cap * 128, cudaMemcpyDeviceToDevice, st));
+    if (wide_slot) EGR_CUDA_TRY(cudaMemcpyAsync(wide_slot, v.wide_slot, (size_t)L.num_nodes * 4, cudaMemcpyDeviceToDevice, st));
+    if (num_wide) EGR_CUDA_TRY(cudaMemcpyAsync(num_wide, v.num_wide, 4, cudaMemcpyDeviceToDevice, st));
+    return EGR_OK;
+}
+extern "C" uint32_t egr_bvh_wide_capacity(uint32_t n) { return n ? wide_capacity(n) : 0; }
 
 // ---------------------------------------------------------------------------------------------------------
 // Mean squared distance to the three nearest neighbours: replaces `distCUDA2` of the reference's
@@ -515,7 +607,7 @@ __global__ void __launch_bounds__(256) k_knn3(BvhView bvh, float *__restrict__ o
 
 }  // namespace egr
 
-extern "C" size_t egr_knn3_scratch_bytes(uint32_t n) { return align_up(bvh_layout(n).total, 256) + build_scratch_layout(n).total; }
+extern "C" size_t egr_knn3_scratch_bytes(uint32_t n) { return align_up(bvh_layout(n, false).total, 256) + build_scratch_layout(n).total; }
 
 extern "C" int egr_knn3_mean_dist2(const float *points, uint32_t n, float *out, void *scratch, size_t scratch_bytes,
                                    void *stream) {
@@ -538,9 +630,9 @@ extern "C" int egr_knn3_mean_dist2(const float *points, uint32_t n, float *out, 
         return EGR_EINVAL;
     }
     cudaStream_t st = (cudaStream_t)stream;
-    BvhView v = bvh_view(scratch, n);
+    BvhView v = bvh_view(scratch, n, false);  // the point tree needs no wide nodes
     const BuildScratch B = build_scratch_layout(n);
-    int rc = build_topology(points, n, v, B, (char *)scratch + align_up(bvh_layout(n).total, 256), st);
+    int rc = build_topology(points, n, v, B, (char *)scratch + align_up(bvh_layout(n, false).total, 256), st);
     if (rc) return rc;
     k_knn_leaves<<<(n + 255) / 256, 256, 0, st>>>(v, points);
     k_knn3<<<(n + 255) / 256, 256, 0, st>>>(v, out);

@@ -57,13 +57,27 @@ __host__ __device__ inline size_t align_up(size_t v, size_t a) { return (v + a -
 // left child of an internal node is node+1 and `skip` is the first node after the subtree, which makes the
 // traversal stackless (one index per warp).
 struct BvhLayout {
-    size_t sorted_ids, records, rawgeo, appearance, nodes, parents, leaf_node, flags, bounds, total;
-    uint32_t n, num_nodes;
+    size_t sorted_ids, records, rawgeo, appearance, nodes, parents, leaf_node, flags, bounds, wide, wide_slot, total;
+    uint32_t n, num_nodes, wide_cap;
 };
-__host__ __device__ inline BvhLayout bvh_layout(uint32_t n) {
+// The 4-wide tree of the per-lane walk (incoherent rays): every second level of the binary tree collapsed, built next
+// to it.  A wide node is 128 B (one cache line): 4 x (child bmin.xyz, .w) (child bmax.xyz, .w); the four .w of the
+// bmin quads hold the child links.  A link is either the index of a wide node, or WIDE_RANGE | (count-1) << 27 | first
+// leaf for a subtree of <= WIDE_FAT leaves (a contiguous range of the Morton-ordered records), or WIDE_NONE (empty
+// slot: its box is inverted and never hit).  Children are in leaf order.
+#ifndef EGR_WIDE_FAT
+#define EGR_WIDE_FAT 16
+#endif
+constexpr uint32_t WIDE_FAT = EGR_WIDE_FAT;      // <= 16 (4 bits of the range link), and a 2 x 16 survivor mask per round
+constexpr uint32_t WIDE_RANGE = 0x80000000u, WIDE_NONE = 0xFFFFFFFFu;
+constexpr uint32_t WIDE_CNT_SHIFT = WIDE_FAT > 16 ? 26 : 27;  // a range link = WIDE_RANGE | (count-1) << shift | first leaf
+constexpr uint32_t WIDE_MAX_GAUSSIANS = 1u << WIDE_CNT_SHIFT;
+__host__ __device__ inline uint32_t wide_capacity(uint32_t n) { return n / 2 + 2; }  // a wide node with one wide child peels >= 2 leaves
+__host__ __device__ inline BvhLayout bvh_layout(uint32_t n, bool with_wide = true) {
     BvhLayout L;
     L.n = n;
     L.num_nodes = n ? 2 * n - 1 : 0;
+    L.wide_cap = with_wide && n ? wide_capacity(n) : 0;
     size_t o = 0;
     L.bounds = o, o = align_up(o + 64, 256);
     L.sorted_ids = o, o = align_up(o + (size_t)n * 4, 256);
@@ -74,12 +88,14 @@ __host__ __device__ inline BvhLayout bvh_layout(uint32_t n) {
     L.parents = o, o = align_up(o + (size_t)L.num_nodes * 4, 256);
     L.leaf_node = o, o = align_up(o + (size_t)n * 4, 256);
     L.flags = o, o = align_up(o + (size_t)L.num_nodes * 4, 256);
+    L.wide = o, o = align_up(o + (size_t)L.wide_cap * 128, 256);
+    L.wide_slot = o, o = align_up(o + (size_t)(L.wide_cap ? L.num_nodes : 0) * 4, 256);
     L.total = o;
     return L;
 }
 struct BvhView {
-    uint32_t n, num_nodes;
-    float *bounds;          // [6] scene bounds of the means (min xyz, max xyz) used for the Morton grid
+    uint32_t n, num_nodes, wide_cap;
+    float *bounds;          // [6] scene bounds of the means (min xyz, max xyz) used for the Morton grid; [8] = num_wide (uint)
     uint32_t *sorted_ids;   // [n] leaf j -> Gaussian id
     float4 *records;        // [n][4] geometry record in leaf order (layout: eval_hit below)
     float4 *rawgeo;         // [n][2] raw quaternion | exp(log-scale), 1/|q| in leaf order (the backward's second gather by leaf)
@@ -88,12 +104,15 @@ struct BvhView {
     uint32_t *parents;      // [num_nodes] preorder index of the parent
     uint32_t *leaf_node;    // [n] preorder index of leaf j
     uint32_t *flags;        // [num_nodes] refit arrival counters (self-resetting)
+    float4 *wide;           // [wide_cap][8] 4-wide nodes (see above); [0] is the root
+    uint32_t *wide_slot;    // [num_nodes] 4 * wide node + slot that mirrors this binary node's box (WIDE_NONE: none)
+    uint32_t *num_wide;     // [1] wide nodes in use (0: the whole tree is one range)
 };
-inline BvhView bvh_view(void *storage, uint32_t n) {
-    BvhLayout L = bvh_layout(n);
+inline BvhView bvh_view(void *storage, uint32_t n, bool with_wide = true) {
+    BvhLayout L = bvh_layout(n, with_wide);
     char *b = (char *)storage;
     BvhView v;
-    v.n = n, v.num_nodes = L.num_nodes;
+    v.n = n, v.num_nodes = L.num_nodes, v.wide_cap = L.wide_cap;
     v.bounds = (float *)(b + L.bounds);
     v.sorted_ids = (uint32_t *)(b + L.sorted_ids);
     v.records = (float4 *)(b + L.records);
@@ -103,6 +122,9 @@ inline BvhView bvh_view(void *storage, uint32_t n) {
     v.parents = (uint32_t *)(b + L.parents);
     v.leaf_node = (uint32_t *)(b + L.leaf_node);
     v.flags = (uint32_t *)(b + L.flags);
+    v.wide = (float4 *)(b + L.wide);
+    v.wide_slot = L.wide_cap ? (uint32_t *)(b + L.wide_slot) : nullptr;
+    v.num_wide = (uint32_t *)(b + L.bounds) + 8;
     return v;
 }
 

@@ -188,10 +188,14 @@ __device__ __forceinline__ void traverse(
     }
 }
 
-// Per-lane stackless walk for incoherent rays (bounce steps): every lane follows its own node index through the
-// same preorder layout ("while-while": each lane runs to its next candidate leaf, then the warp processes the
-// leaves together).  The union walk above would make every lane test every node any lane needs, which is 32x
-// redundant once the rays of a warp fan out.
+// Per-lane walk for incoherent rays (bounce steps): every lane follows its own path through the 4-WIDE tree (every
+// second level of the binary tree collapsed, egr_common.cuh) with a small stack of pending child links ("while-while":
+// each lane runs to its next candidate ranges, then the warp processes the ranges together).  The union walk above
+// would make every lane test every node any lane needs, which is 32x redundant once the rays of a warp fan out; and a
+// binary walk costs one dependent 32-byte gather per level, where a wide node fetches four boxes with one cache line:
+// half as many dependent round trips to reach a range, and ranges of <= WIDE_FAT leaves instead of <= 32 (fewer
+// bounding-sphere tests per range).  Children are visited in slot order = leaf order, so hits are still found in
+// ascending leaf index (the order of the transmittance product and of the tie-break).
 constexpr uint32_t NO_LEAF = 0xFFFFFFFFu;
 #ifdef EGR_TASK_CLOCKS
 __shared__ uint32_t s_dbg_nodes[128], s_dbg_rounds[128];
@@ -201,9 +205,6 @@ __shared__ long long s_dbg_tnode[4], s_dbg_tcand[4];
 #else
 #define EGR_DBG_NODE()
 #define EGR_DBG_ROUND()
-#endif
-#ifndef EGR_FAT_LANE
-#define EGR_FAT_LANE 32
 #endif
 #ifndef EGR_SELBATCH
 #define EGR_SELBATCH 4
@@ -217,14 +218,33 @@ __shared__ long long s_dbg_tnode[4], s_dbg_tcand[4];
 #ifndef EGR_QBATCH
 #define EGR_QBATCH 8
 #endif
-constexpr uint32_t FAT_LANE = EGR_FAT_LANE;  // <= 32: the survivors of one range are a 32-bit mask
+// Pending links of one lane.  The binary tree is at most 64 + 30 levels deep (Morton bits + index tie-break), a wide
+// level spans two of them and leaves at most 3 pending siblings behind: 47 * 3 entries bound the stack.
+constexpr int WIDE_STACK = 144;
+
+// slab test of one ray against the box (lo, hi); [tlo, thi] is the part of the ray that matters (see traverse())
+__device__ __forceinline__ bool box_hit(const float4 lo, const float4 hi, const f3 o, const f3 idir, const float tlo, const float thi) {
+    if (!(lo.x <= hi.x)) return false;  // empty (invisible subtree, unused slot)
+    const float t0x = (lo.x - o.x) * idir.x, t1x = (hi.x - o.x) * idir.x;
+    const float t0y = (lo.y - o.y) * idir.y, t1y = (hi.y - o.y) * idir.y;
+    const float t0z = (lo.z - o.z) * idir.z, t1z = (hi.z - o.z) * idir.z;
+    float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
+    float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
+    tn = tn * (tn >= 0.0f ? 0.9999996f : 1.0000004f);  // NaN-safe widening, see traverse()
+    tf = tf * (tf >= 0.0f ? 1.0000004f : 0.9999996f);
+    return fmaxf(tn, tlo) <= fminf(tf, thi);
+}
+
 template <bool PASS0>
 __device__ __forceinline__ void traverse_lane(
     const BvhView &bvh, const StepCfg &sc, const f3 o, const f3 d, const f3 idir, const bool active, const float w,
     LaneList &L, float &T_full, int &n_acc, int &n_trav) {
-    const uint32_t end = bvh.num_nodes;
-    const float4 *__restrict__ nodes = bvh.nodes;
-    uint32_t node = active ? 0u : end;
+    const float4 *__restrict__ wide = bvh.wide;
+    uint32_t stack[WIDE_STACK];
+    int sp = 0;
+    // the whole tree is one range when it has no wide node (<= WIDE_FAT Gaussians)
+    const uint32_t nw = *bvh.num_wide;
+    uint32_t cur = !active ? WIDE_NONE : (nw ? 0u : (WIDE_RANGE | ((bvh.n - 1) << WIDE_CNT_SHIFT)));
     while (true) {
         // every lane walks on until it holds TWO candidate ranges (or its walk ends): half as many warp-wide
         // rounds, and a lane that finds its ranges early waits for fewer node visits of the others
@@ -233,42 +253,39 @@ __device__ __forceinline__ void traverse_lane(
         __syncwarp();
         const long long ta_ = clock64();
 #endif
-        while (node < end) {
+        while (true) {
+            if (cur == WIDE_NONE) {
+                if (sp == 0) break;
+                cur = stack[--sp];
+            }
+            if (cur & WIDE_RANGE) {  // a subtree of <= WIDE_FAT leaves: a contiguous record range, tested directly
+                const uint32_t first = cur & (WIDE_MAX_GAUSSIANS - 1u), cnt = ((cur & ~WIDE_RANGE) >> WIDE_CNT_SHIFT) + 1u;
+                EGR_CHECK(first + cnt <= bvh.n);
+                cur = WIDE_NONE;
+                if (leaf == NO_LEAF) {
+                    leaf = first, leaf_n = cnt;
+                    continue;
+                }
+                leaf2 = first, leaf2_n = cnt;
+                break;
+            }
             EGR_DBG_NODE();
-            float4 A, B;
-            ldg2(&nodes[2 * (size_t)node], A, B);
-            bool hit = false;
-            if (A.x <= B.x) {
-                float t0x = (A.x - o.x) * idir.x, t1x = (B.x - o.x) * idir.x;
-                float t0y = (A.y - o.y) * idir.y, t1y = (B.y - o.y) * idir.y;
-                float t0z = (A.z - o.z) * idir.z, t1z = (B.z - o.z) * idir.z;
-                float tn = fmaxf(fmaxf(fminf(t0x, t1x), fminf(t0y, t1y)), fminf(t0z, t1z));
-                float tf = fminf(fminf(fmaxf(t0x, t1x), fmaxf(t0y, t1y)), fmaxf(t0z, t1z));
-                tn = tn * (tn >= 0.0f ? 0.9999996f : 1.0000004f);  // NaN-safe widening, see traverse()
-                tf = tf * (tf >= 0.0f ? 1.0000004f : 0.9999996f);
-                float lo = PASS0 ? 0.0f : fmaxf(sc.tmin, w);  // see traverse()
-                float hi = PASS0 ? FLT_MAX : (L.cnt < LIST_CAP ? sc.tmax : fminf(sc.tmax, L.maxt));
-                hit = fmaxf(tn, lo) <= fminf(tf, hi);
-            }
-            if (!hit) {
-                node = __float_as_uint(A.w);
-                continue;
-            }
-            const uint32_t skip = __float_as_uint(A.w), tag = __float_as_uint(B.w);
-            const uint32_t nl = (skip - node + 1) >> 1;
-            if (nl > FAT_LANE) {
-                node = node + 1;
-                continue;
-            }
-            // small subtree: its Gaussians are a contiguous record range, tested directly instead of descending
-            EGR_CHECK(nl >= 1 && (tag & ~FIRST_LEAF_FLAG) + nl <= bvh.n && skip > node && skip <= end);
-            node = skip;
-            if (leaf == NO_LEAF) {
-                leaf = tag & ~FIRST_LEAF_FLAG, leaf_n = nl;
-                continue;
-            }
-            leaf2 = tag & ~FIRST_LEAF_FLAG, leaf2_n = nl;
-            break;
+            EGR_CHECK(cur < nw);
+            const float4 *wn = wide + 8 * (size_t)cur;
+            float4 b0, b1, b2, b3, b4, b5, b6, b7;  // one 128-byte line: four boxes, links in the .w of the bmin quads
+            ldg2(wn, b0, b1), ldg2(wn + 2, b2, b3), ldg2(wn + 4, b4, b5), ldg2(wn + 6, b6, b7);
+            const float tlo = PASS0 ? 0.0f : fmaxf(sc.tmin, w);  // see traverse()
+            const float thi = PASS0 ? FLT_MAX : (L.cnt < LIST_CAP ? sc.tmax : fminf(sc.tmax, L.maxt));
+            const bool h0 = box_hit(b0, b1, o, idir, tlo, thi), h1 = box_hit(b2, b3, o, idir, tlo, thi);
+            const bool h2 = box_hit(b4, b5, o, idir, tlo, thi), h3 = box_hit(b6, b7, o, idir, tlo, thi);
+            const uint32_t l0 = __float_as_uint(b0.w), l1 = __float_as_uint(b2.w), l2 = __float_as_uint(b4.w), l3 = __float_as_uint(b6.w);
+            // the first hit child is visited next, the others wait on the stack in reverse order
+            cur = WIDE_NONE;
+            EGR_CHECK(sp + 3 <= WIDE_STACK);
+            if (h3) cur = l3;
+            if (h2) { if (cur != WIDE_NONE) stack[sp++] = cur; cur = l2; }
+            if (h1) { if (cur != WIDE_NONE) stack[sp++] = cur; cur = l1; }
+            if (h0) { if (cur != WIDE_NONE) stack[sp++] = cur; cur = l0; }
         }
 #ifdef EGR_TASK_CLOCKS
         __syncwarp();

@@ -480,6 +480,19 @@ class Raytracer:
                                              self._stream()))
         return ids, rec, nodes, par
 
+    def export_wide_bvh(self):
+        """Copies of the 4-wide tree of the bounce walk: (wide [num_wide,32] float32, wide_slot [2n-1] int32)."""
+        self._check_bvh_current()
+        n = self.gaussian_data.count
+        cap = int(self._lib.egr_bvh_wide_capacity(n))
+        wide = torch.empty(cap, 32, dtype=torch.float32, device=self._dev)
+        slot = torch.empty(max(2 * n - 1, 0), dtype=torch.int32, device=self._dev)
+        num = torch.zeros(1, dtype=torch.int32, device=self._dev)
+        _capi.check(self._lib.egr_bvh_export_wide(self._bvh_storage.data_ptr(), self._bvh_storage.numel(), n,
+                                                  wide.data_ptr(), slot.data_ptr(), num.data_ptr(), self._stream()))
+        k = int(num.item())
+        return wide[:k], slot
+
     def export_hit_lists(self, step, cap):
         """Per-pixel composited Gaussian ids / distances of the last grad-mode raytrace() at ``step``."""
         P = self.width * self.height

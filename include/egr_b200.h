@@ -340,6 +340,15 @@ int egr_adam_step(float *grad_records, uint32_t count, const EgrGradTargets *par
 int egr_bvh_export(const void *storage, size_t storage_bytes, uint32_t num_gaussians, uint32_t *sorted_ids,
                    float *records, float *nodes, uint32_t *parents, void *stream);
 
+/* The 4-wide tree the bounce steps walk (every second level of the binary tree collapsed; built by egr_bvh_build,
+ * boxes refreshed by every egr_bvh_refit): wide [cap,32] floats = 4 x (child bmin.xyz, link bits) (child bmax.xyz, -),
+ * wide_slot [2n-1] = for every binary node the slot (4 * wide node + child) that mirrors its box (0xFFFFFFFF: none),
+ * *num_wide = nodes in use; cap = egr_bvh_wide_capacity(num_gaussians).  A link is a wide-node index, or
+ * 0x80000000 | (count-1) << 27 | first leaf for a subtree of <= 16 leaves, or 0xFFFFFFFF (empty slot). */
+uint32_t egr_bvh_wide_capacity(uint32_t num_gaussians);
+int egr_bvh_export_wide(const void *storage, size_t storage_bytes, uint32_t num_gaussians, float *wide,
+                        uint32_t *wide_slot, uint32_t *num_wide, void *stream);
+
 /* Decode the hit log of the last grads-enabled egr_raytrace: per pixel, the ORIGINAL Gaussian ids (and distances)
  * of the hits composited at `step`, in composite order; ids/ts are [H*W, cap], counts [H*W] (not capped).
  * Plays the role of walking the reference's backward per-pixel linked list (per_pixel_linked_list.h:19-75). */

@@ -61,6 +61,49 @@ def test_lbvh_indices_bit_exact(small):
     assert (bmin[leaf_nodes] <= mu).all() and (bmax[leaf_nodes] >= mu).all()
 
 
+def test_wide_tree_covers_every_leaf_once_in_order(small):
+    """The 4-wide tree of the bounce walk: walking it from the root in slot order yields ranges that tile the Morton
+    order [0, n) exactly once, ascending (the order of the transmittance product); every slot's box is the box of the
+    binary node behind it; ranges hold at most 16 leaves."""
+    import torch
+
+    sc, cam, W, Hh = small
+    n = sc["mean"].shape[0]
+    for count in (n, 17, 16, 5, 1):
+        sub = {k: v[:count] for k, v in sc.items()}
+        rt = H.make_gpu_raytracer(sub, cam, dict(num_bounces=0))
+        _, _, nodes, _ = rt.export_bvh()
+        wide, slot = rt.export_wide_bvh()
+        torch.cuda.synchronize()
+        nodes, wide, slot = nodes.cpu().numpy(), wide.cpu().numpy(), slot.cpu().numpy().astype(np.uint32)
+        if count <= 16:
+            assert wide.shape[0] == 0  # the whole tree is one range
+            continue
+        links = wide.reshape(-1, 4, 8)[:, :, 3].copy().view(np.uint32)
+        behind = {int(s_): e for e, s_ in enumerate(slot) if s_ != 0xFFFFFFFF}  # slot -> binary node it mirrors
+        covered, stack = [], [np.uint32(0)]
+        visited = 0
+        while stack:
+            cur = int(stack.pop())
+            if cur & 0x80000000:
+                covered.append((cur & 0x07FFFFFF, ((cur >> 27) & 15) + 1))
+                continue
+            visited += 1
+            for i in (3, 2, 1, 0):
+                if links[cur, i] != 0xFFFFFFFF:
+                    stack.append(links[cur, i])
+                    e = behind[4 * cur + i]
+                    assert np.array_equal(wide[cur, 8 * i:8 * i + 3], nodes[e, 0:3]) and np.array_equal(wide[cur, 8 * i + 4:8 * i + 7], nodes[e, 4:7])
+                else:
+                    assert 4 * cur + i not in behind and wide[cur, 8 * i] > wide[cur, 8 * i + 4]  # inverted box
+        assert visited == wide.shape[0]
+        pos = 0
+        for first, cnt in covered:
+            assert first == pos and 1 <= cnt <= 16
+            pos += cnt
+        assert pos == count
+
+
 def test_geometry_records_match_oracle(small):
     sc, cam, W, Hh = small
     rt = H.make_gpu_raytracer(sc, cam, dict(num_bounces=0))

@@ -55,7 +55,7 @@ def test_size_queries_and_argument_errors_without_gpu():
     lib = _capi.load()
     assert lib.egr_bvh_storage_bytes(0) < lib.egr_bvh_storage_bytes(1) < lib.egr_bvh_storage_bytes(1000)
     per = (lib.egr_bvh_storage_bytes(2_000_000) - lib.egr_bvh_storage_bytes(1_000_000)) / 1e6
-    assert 64 + 32 + 48 + 64 + 4 * 4 <= per <= 240  # records + raw geometry + appearance + 2 nodes + index arrays per Gaussian
+    assert 64 + 32 + 48 + 64 + 4 * 4 <= per <= 310  # records + raw geometry + appearance + 2 nodes + index arrays + wide nodes (worst case n/2 x 144 B) per Gaussian
     assert lib.egr_pixel_state_bytes(800, 800, 3) >= 40 * 3 * 640000 * 4
     assert lib.egr_hitlog_bytes_for_hits(512) == 128 + 16 * 32 * 8  # {leaf, T_after} per logged hit
     assert lib.egr_raytrace(None, 0, None) == -1 and b"null" in lib.egr_last_error()
