@@ -191,8 +191,11 @@ def run_ours(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    registered = False
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        if args.nccl_register:
+            registered = distributed.use_registered_gradient_records()
     peak_gbs, peak_kind = _peaks()
 
     cf = CONFIGS[args.config]
@@ -429,7 +432,7 @@ def run_ours(args):
     # all-reduce of the gradient record (world > 1) -> the fused optimiser step (gradient import + scale decay + Adam
     # + clamps + zeroing).  Each step's parameters feed the next export.  The prune -> compact -> rebind -> resize ->
     # export -> rebuild pipeline of every `pruning_interval`-th iteration is timed once and amortised.
-    train = None
+    train = tr = None
     if GRADS and not args.no_train:
         from egr_b200 import trainer as trainer_mod
 
@@ -490,7 +493,8 @@ def run_ours(args):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": cf["workload"], "num_gaussians": N, "resolution": [Wd, Hd], "views": len(cams),
                        "views_per_step": world, "sharding": "views sharded over ranks, scene+BVH replicated, one "
-                       "all-reduce of the flat [N,24] gradient record" if world > 1 else "single GPU",
+                       "all-reduce of the flat [N,24] gradient record" + (" (NCCL-registered buffer)" if registered else "")
+                       if world > 1 else "single GPU",
                        "l2": "inputs larger than L2: >400 MB of records/nodes/params/state/hit log touched per step, "
                              "a different view every step", "hitlog_overflow": overflow},
             "clocks": clocks, "e2e": e2e, "gpu_launches": n_launch * K,
@@ -498,6 +502,16 @@ def run_ours(args):
         }
         print(json.dumps(line))
     if world > 1:
+        if registered:
+            # the registered pool frees its memory through NCCL: drop every tensor that lives in it first
+            sys.stdout.flush()
+            del g, tr, rtr, rt, pc
+            import gc
+
+            gc.collect()
+            torch.cuda.synchronize()
+            distributed.release_registered_pools()
+            torch.cuda.empty_cache()
         dist.destroy_process_group()
 
 
@@ -511,6 +525,7 @@ def main():
     ap.add_argument("--num-gaussians", type=int, default=0, help="override the config's Gaussian count")
     ap.add_argument("--res", type=int, default=0, help="override the config's resolution (square)")
     ap.add_argument("--no-train", action="store_true", help="skip the train-iteration leg")
+    ap.add_argument("--nccl-register", type=int, default=1, help="1: gradient record from NCCL's allocator, registered (multi-GPU)")
     ap.add_argument("--hitlog-hits", type=int, default=120_000_000)
     ap.add_argument("--cpu-pixels", type=int, default=2048)
     ap.add_argument("--no-cpu", action="store_true")

@@ -34,3 +34,53 @@ def max_over_ranks(value_ms: float, device) -> float:
     t = torch.tensor([value_ms], dtype=torch.float64, device=device)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return float(t.item())
+
+
+_pools = []  # registered pools stay alive (and registered) for the life of the process group
+
+
+def use_registered_gradient_records(group=None) -> bool:
+    """From now on the tracer's flat gradient record is allocated from NCCL's allocator (``ncclMemAlloc``) in a memory
+    pool registered with the communicator, which lets NCCL run the all-reduce on user buffers (no staging copies) and
+    through the NVSwitch reduction (NVLS) where the fabric offers it.  Returns False -- and changes nothing -- when the
+    backend does not expose the allocator (CPU / gloo, older builds).  Call it after ``init_process_group`` and before
+    the ``Raytracer`` is constructed; ``resize()`` allocates the new record from the same pool."""
+    from . import _capi, raytracer
+
+    if not dist.is_available() or not dist.is_initialized() or not torch.cuda.is_available():
+        return False
+    try:
+        dev = torch.device("cuda", torch.cuda.current_device())
+        backend = (group or dist.group.WORLD)._get_backend(dev)
+        pool = torch.cuda.MemPool(backend.mem_allocator)
+    except Exception:
+        return False
+
+    def alloc(n, device):
+        with torch.cuda.use_mem_pool(pool):
+            t = torch.zeros(n, _capi.EGR_GRAD_STRIDE, dtype=torch.float32, device=device)
+        try:
+            backend.register_mem_pool(pool)  # (re-)registers the pool's segments, the new one included
+        except Exception:
+            pass
+        return t
+
+    _pools.append((pool, backend))
+    raytracer.GRAD_RECORD_ALLOCATOR = alloc
+    return True
+
+
+def release_registered_pools() -> None:
+    """Deregister the pools made by :func:`use_registered_gradient_records` and restore the default allocator.  Call it
+    before ``destroy_process_group`` (the pools free their memory through NCCL, which needs a live communicator);
+    tensors allocated from the pools must not be used afterwards."""
+    from . import raytracer
+
+    raytracer.GRAD_RECORD_ALLOCATOR = raytracer._default_record_allocator
+    while _pools:
+        pool, backend = _pools.pop()
+        try:
+            backend.deregister_mem_pool(pool)
+        except Exception:
+            pass
+        del pool

@@ -126,6 +126,15 @@ GRAD_COLUMNS = dict(mean=(0, 3), opacity=(3, 1), scale=(4, 3), roughness=(7, 1),
 PARAM_CHANNELS = dict(rgb=3, normal=3, f0=3, roughness=1, opacity=1, scale=3, mean=3, rotation=4)
 
 
+# Allocator of the flat gradient record.  A multi-GPU job may replace it (distributed.use_registered_gradient_records)
+# so that the one buffer the ranks all-reduce comes from NCCL's own allocator and is registered with the communicator.
+def _default_record_allocator(n, dev):
+    return torch.zeros(n, _capi.EGR_GRAD_STRIDE, dtype=torch.float32, device=dev)
+
+
+GRAD_RECORD_ALLOCATOR = _default_record_allocator
+
+
 class GaussianDataHolder(_Holder):  # gaussians.h:30-135
     def __init__(self, dev):
         self._dev = dev
@@ -136,7 +145,7 @@ class GaussianDataHolder(_Holder):  # gaussians.h:30-135
 
     def _bind_grads(self, n):
         # ONE flat buffer; the reference's dL_d* tensors and total_weight are strided views of it
-        self.grad_records = torch.zeros(n, _capi.EGR_GRAD_STRIDE, dtype=torch.float32, device=self._dev)
+        self.grad_records = GRAD_RECORD_ALLOCATOR(n, self._dev)
         for name, (c0, ch) in GRAD_COLUMNS.items():
             view = self.grad_records[:, c0:c0 + ch]
             if name == "total_weight":
