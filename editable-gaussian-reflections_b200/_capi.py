@@ -59,7 +59,7 @@ class EgrGaussians(C.Structure):
 
 class EgrParams(C.Structure):
     _fields_ = [
-        ("image_width", C.c_uint32), ("image_height", C.c_uint32), ("num_steps", C.c_uint32), ("reserved0", C.c_uint32),
+        ("image_width", C.c_uint32), ("image_height", C.c_uint32), ("num_steps", C.c_uint32), ("tile_rows", C.c_uint32),
         ("camera", EgrCamera), ("config", EgrConfig), ("framebuffer", EgrFramebuffer), ("gaussians", EgrGaussians),
         ("metadata", EgrMetadata), ("stats", EgrStats),
         ("bvh_storage", _FP), ("bvh_storage_bytes", C.c_size_t),

@@ -724,13 +724,16 @@ __global__ void __launch_bounds__(32 * WARPS, (LANE_WALK ? EGR_LANE_WARPS : 20) 
     const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int B = min(*c.p.config.num_bounces, (int)c.S - 1);  // shaders.cu:85
     if (step > B) return;
-    const uint32_t groups = step == 0 ? c.num_warps : (c.ray_count[step] + 31) / 32;
+    // step 0: the 8x4 tiles of the image, or of the band of tile rows this call is restricted to (EgrParams.tile_rows)
+    const uint32_t g_first = step == 0 ? c.tile_first : 0u;
+    const uint32_t groups = step == 0 ? c.tile_count : (c.ray_count[step] + 31) / 32;
     char *list = c.hitlist + (size_t)(blockIdx.x * WARPS + wib) * HITLIST_WARP_BYTES;
     while (true) {
         uint32_t g = 0;
         if (lane == 0) g = atomicAdd(&c.work_counter[step], 1u);
         g = __shfl_sync(0xffffffffu, g, 0);
         if (g >= groups) break;
+        g += g_first;
 #ifdef EGR_TASK_CLOCKS
         s_dbg_nodes[threadIdx.x] = 0, s_dbg_rounds[threadIdx.x] = 0;
         if (lane == 0) s_dbg_tnode[wib] = 0, s_dbg_tcand[wib] = 0;
@@ -852,6 +855,15 @@ static int make_ctx(const EgrParams *p, TraceCtx &c) {
     c.work_counter = (uint32_t *)(sb + L.work_counter);
     c.hitlist = sb + L.hitlist;
     c.P = L.P, c.S = L.S, c.tiles_x = tiles_x(p->image_width), c.num_warps = L.num_warps;
+    c.tile_first = 0, c.tile_count = L.num_warps;
+    if (p->tile_rows) {
+        const uint32_t r0 = p->tile_rows & 0xFFFFu, r1 = p->tile_rows >> 16, rows = tiles_y(p->image_height);
+        if (r0 >= r1 || r1 > rows) {
+            set_error("tile_rows: band [%u, %u) is not inside the image's %u tile rows", r0, r1, rows);
+            return EGR_EINVAL;
+        }
+        c.tile_first = r0 * c.tiles_x, c.tile_count = (r1 - r0) * c.tiles_x;
+    }
     static const int force_walk_env = [] {  // debugging aid, read once: 1 = warp-uniform walk everywhere, 2 = per-lane
         const char *e = getenv("EGR_FORCE_WALK");
         return e ? atoi(e) : 0;

@@ -17,6 +17,7 @@ struct TraceCtx {
     uint32_t *work_counter;    // [S] next 32-ray group of the persistent forward launch
     char *hitlist;             // [resident warps][HITLIST_WARP_BYTES] hit lists of the rays being traced (egr_common.cuh)
     uint32_t P, S, tiles_x, num_warps;
+    uint32_t tile_first, tile_count;  // step 0 traces the 8x4 tiles [tile_first, tile_first + tile_count) (a band of tile rows)
     uint32_t hitlog_chunks;    // capacity in chunks
     int force_walk;            // 0 = auto (warp-uniform walk for step 0, per-lane for bounces)
 };

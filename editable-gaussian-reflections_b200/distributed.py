@@ -18,6 +18,34 @@ def shard_views(num_views: int, rank: int, world_size: int, step: int):
     return (step * world_size + rank) % num_views
 
 
+def band_for_rank(image_height: int, rank: int, world_size: int):
+    """Rows [begin, end) of the horizontal band rank ``rank`` traces when ONE view is split over ``world_size`` GPUs
+    (the secondary split of SURVEY 8e: re-render latency of an edit, exact single-view semantics).  Bands are whole
+    4-pixel tile rows, as even as possible; feed them to ``Raytracer.set_pixel_band``."""
+    rows = (image_height + 3) // 4
+    lo, hi = rows * rank // world_size, rows * (rank + 1) // world_size
+    return 4 * lo, min(4 * hi, image_height)
+
+
+def gather_bands(plane: torch.Tensor, image_height: int, group=None) -> torch.Tensor:
+    """Assemble a framebuffer plane ``[S,H,W,C]`` (or ``[1,H,W,C]``) whose rows were traced band-wise: every rank
+    contributes the rows of its own band (one all-gather of equal-sized padded bands)."""
+    if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return plane
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    bands = [band_for_rank(image_height, r, world) for r in range(world)]
+    hmax = max(b - a for a, b in bands)
+    a, b = bands[rank]
+    mine = torch.zeros(plane.shape[0], hmax, *plane.shape[2:], dtype=plane.dtype, device=plane.device)
+    mine[:, : b - a] = plane[:, a:b]
+    parts = [torch.empty_like(mine) for _ in range(world)]
+    dist.all_gather(parts, mine, group=group)
+    out = torch.empty_like(plane)
+    for (a, b), part in zip(bands, parts):
+        out[:, a:b] = part[:, : b - a]
+    return out
+
+
 def allreduce_gradients(grad_records: torch.Tensor, group=None, async_op: bool = False):
     """Sum the flat gradient record over all ranks, in place.  One call covers all 22 floats per Gaussian."""
     if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:

@@ -332,6 +332,7 @@ class Raytracer:
         """Capture the raw pointers once (raytracer.cpp:59-68); refreshed by resize()/rebuild_bvh()."""
         p = _capi.EgrParams()
         p.image_width, p.image_height, p.num_steps = self.width, self.height, self._S
+        p.tile_rows = getattr(self, "_tile_rows", 0)
         for f in _capi.CAMERA_FIELDS:
             setattr(p.camera, f, getattr(self.camera_data, f).data_ptr())
         p.config = self._config_struct()
@@ -461,6 +462,19 @@ class Raytracer:
         g = self.gaussian_data
         _capi.check(self._lib.egr_gradients_accumulate(g.grad_records.data_ptr(), int(g.grad_records.shape[0]),
                                                        C.byref(t), self._stream()))
+
+    def set_pixel_band(self, row_begin: int | None = None, row_end: int | None = None):
+        """Restrict the following raytrace() calls to the pixel rows [row_begin, row_end) (``row_begin`` a multiple of 4,
+        ``row_end`` a multiple of 4 or the image height); ``None`` = the whole image again.  Not in the reference: it
+        is how ONE view is split over several GPUs (``distributed.band_for_rank``): the bands of all ranks tile the
+        single-GPU image bit for bit, and the all-reduced gradient record equals the single-GPU gradients."""
+        if row_begin is None:
+            self._tile_rows = 0
+        else:
+            if row_begin % 4 or (row_end % 4 and row_end != self.height) or not (0 <= row_begin < row_end <= self.height):
+                raise RuntimeError("pixel band: rows must be multiples of 4 inside the image")
+            self._tile_rows = (row_begin // 4) | (((row_end + 3) // 4) << 16)
+        self._build_params()
 
     def set_ray_override(self, ray_origin=None, ray_direction=None, step_executed=None):
         """Test input: rays of the steps >= 1 ([S,H,W,3] each) and which steps run ([S,H,W] int32), e.g. the bounce

@@ -119,7 +119,12 @@ typedef struct EgrStats {        /* csrc/core/stats.h:3-6 + three extra planes u
 typedef struct EgrParams {       /* csrc/params.h:11-26 */
     uint32_t image_width, image_height;
     uint32_t num_steps;          /* S = MAX_BOUNCES+1 the planes were allocated with (<= EGR_MAX_STEPS) */
-    uint32_t reserved0;
+    uint32_t tile_rows;          /* 0 = the whole image; else (first) | (end << 16) in units of 4-pixel tile rows: only the
+                                  * pixels of rows [4*first, 4*end) are traced (their bounce rays included).  Used to
+                                  * split ONE view over several GPUs by horizontal bands: per-pixel seeds do not depend
+                                  * on the band, so the bands of all ranks tile the single-GPU image bit for bit and the
+                                  * summed gradient records equal the single-GPU gradients (float-atomic order aside).
+                                  * Outside the band the outputs hold the values of a pixel without rays. */
     EgrCamera camera;
     EgrConfig config;
     EgrFramebuffer framebuffer;

@@ -457,6 +457,52 @@ def test_resize_and_empty_and_ragged():
     assert g.rgb.grad.shape == (257, 3) and g.rgb.grad.data_ptr() == g.dL_drgb.data_ptr()
 
 
+def test_pixel_bands_tile_the_image_and_sum_to_the_full_gradient(small):
+    """ONE view split by horizontal bands (the secondary multi-GPU split, run here band after band on one GPU): inside
+    its band every plane of every step is bit-identical to the full render (seeds depend on the pixel only), outside it
+    nothing is traced, and the gradient records of the bands add up to the record of the full view."""
+    import torch
+
+    from egr_b200 import distributed
+
+    sc, cam, W, Hh = small
+    cfg = dict(num_bounces=2, jitter_primary_rays=True, loss_weight_diffuse=5.0, loss_weight_specular=3.0)
+    rt = H.make_gpu_raytracer(sc, cam, cfg)
+    H.set_targets(rt, scenes.random_targets(W, Hh, seed=8))
+    g = rt.get_gaussians()
+
+    def run(band):
+        rt.set_pixel_band(*band) if band else rt.set_pixel_band(None)
+        rt.get_metadata().total_num_calls.zero_()
+        with torch.no_grad():
+            rt.raytrace()
+        out = H.gpu_outputs(rt)
+        g.grad_records.zero_()
+        rt.get_metadata().total_num_calls.zero_()
+        with torch.enable_grad():
+            rt.raytrace()
+        torch.cuda.synchronize()
+        return out, g.grad_records.clone()
+
+    full, gfull = run(None)
+    gsum = torch.zeros_like(gfull)
+    world = 3
+    bands = [distributed.band_for_rank(Hh, r, world) for r in range(world)]
+    assert bands[0][0] == 0 and bands[-1][1] == Hh and all(b[1] == c[0] for b, c in zip(bands, bands[1:]))
+    for a, b in bands:
+        out, gb = run((a, b))
+        gsum += gb
+        for k in H.OUT_KEYS:
+            assert np.array_equal(out[k][:, a:b].view(np.uint32), full[k][:, a:b].view(np.uint32)), (k, a, b)
+        assert out["num_steps_per_pixel"][:a].sum() == 0 and out["num_steps_per_pixel"][b:].sum() == 0
+        assert np.array_equal(out["num_steps_per_pixel"][a:b], full["num_steps_per_pixel"][a:b])
+    scale = gfull.abs().amax(dim=0).clamp_min(1e-20)
+    assert float(((gsum - gfull).abs() / scale).max()) <= 1e-4 and float(gfull.abs().max()) > 0
+    rt.set_pixel_band(None)
+    with pytest.raises(RuntimeError):
+        rt.set_pixel_band(2, 10)
+
+
 def test_resize_without_rebuild_is_refused(small):
     """resize() changes the count; the tree still describes the old one until rebuild_bvh(): refit / trace / export
     must refuse instead of reading a foreign layout."""

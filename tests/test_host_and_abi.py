@@ -171,7 +171,14 @@ def _gloo_worker(rank, world, port, q):
         distributed.allreduce_gradients(grads)
         views = [distributed.shard_views(7, rank, world, s) for s in range(7)]
         t = distributed.max_over_ranks(float(rank + 1), torch.device("cpu"))
-        q.put((rank, float(grads[0, 0]), float(grads.sum()), views, t))
+        # one view split into horizontal bands: every rank holds only the rows of its own band
+        Hh, W = 22, 5  # 6 tile rows (the last one ragged) over 2 ranks
+        full = torch.arange(2 * Hh * W * 3, dtype=torch.float32).reshape(2, Hh, W, 3)
+        a, b = distributed.band_for_rank(Hh, rank, world)
+        mine = torch.full_like(full, -1.0)
+        mine[:, a:b] = full[:, a:b]
+        band_ok = bool(torch.equal(distributed.gather_bands(mine, Hh), full))
+        q.put((rank, float(grads[0, 0]), float(grads.sum()), views, t, (a, b), band_ok))
     finally:
         dist.destroy_process_group()
 
@@ -189,8 +196,9 @@ def test_view_sharding_and_gradient_allreduce_gloo_world2():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    for rank, v00, total, views, t in res:
+    for rank, v00, total, views, t, band, band_ok in res:
         assert v00 == 3.0 and total == 3.0 * 240 and t == 2.0  # sum over ranks, max over ranks
+        assert band_ok and band == ((0, 12), (12, 22))[rank]  # whole 4-pixel tile rows, together the whole image
     seen = sorted(res[0][3] + res[1][3])
     assert seen == sorted(list(range(7)) * 2)  # every view visited equally often, ranks never collide in a step
     assert all(a != b for a, b in zip(res[0][3], res[1][3]))

@@ -61,6 +61,7 @@ def _worker(rank, world, port, out_dir):
             gen = torch.Generator(device=dev).manual_seed(100 + rank)  # DIFFERENT rows on every rank ...
             tr.add_points(tr.farfield_points(200 + 50 * rank, extent=1.0, generator=gen))  # ... rank 0's win
     ids, _, _, _ = rt.export_bvh()
+    res["calls_after_training"] = int(rt.get_metadata().total_num_calls)
     mine = [getattr(pc, a) for a in trainer.MODEL_ATTR.values()] + list(tr.optimizer.exp_avg.values()) + \
            list(tr.optimizer.exp_avg_sq.values()) + [ids.float(), rt.get_metadata().total_num_calls.float()]
     flat = torch.cat([t.reshape(-1).float() for t in mine])
@@ -74,6 +75,19 @@ def _worker(rank, world, port, out_dir):
         res["replicas_bit_identical"] = all(bool(torch.equal(other[0], o)) for o in other[1:])
     else:
         res["replicas_bit_identical"] = False
+    # (d) ONE view split into horizontal bands over the ranks: gathered planes == the single-GPU image, bit for bit
+    rtr.import_gradients = False
+    v0 = views[0]
+    with torch.no_grad():
+        rt.get_metadata().total_num_calls.zero_()
+        rt.set_pixel_band(*distributed.band_for_rank(Hh, rank, world))
+        egr_b200.render(v0, rtr, targets_available=False, force_update_bvh=True)
+        fb = rt.get_framebuffer()
+        banded = {k: distributed.gather_bands(getattr(fb, k), Hh) for k in ("output_rgb", "output_depth", "output_final")}
+        rt.set_pixel_band(None)
+        rt.get_metadata().total_num_calls.zero_()
+        egr_b200.render(v0, rtr, targets_available=False)
+        res["bands_equal_full_image"] = all(bool(torch.equal(banded[k], getattr(fb, k))) for k in banded)
     res["count"] = int(pc._xyz.shape[0])
     res["calls"] = int(rt.get_metadata().total_num_calls)
     res["finite"] = bool(torch.isfinite(pc._xyz).all())
@@ -101,5 +115,6 @@ def test_two_rank_nccl_training_keeps_replicas_identical(tmp_path):
     print("two-rank result:", res)
     assert res["allreduce_vs_single_gpu_sum_rel"] <= 1e-4, res
     assert res["replicas_bit_identical"] and len(set(res["sizes"])) == 1, res
-    assert res["calls"] == 6 and res["finite"] and res["overflow"] == 0, res
+    assert res["bands_equal_full_image"], res
+    assert res["finite"] and res["overflow"] == 0 and res["calls_after_training"] == 6, res
     assert 3000 - 2500 < res["count"] < 3000 + 200, res  # pruned some, then rank 0's 200 rows were inserted
