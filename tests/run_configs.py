@@ -188,15 +188,26 @@ def c5(n5):
         res["refit_ms"] = a.elapsed_time(b)
         pc._opacity[sel] = -1e8  # delete (editable_gaussian_model.py:324-328)
         res["delete_refit_render_ms"] = render_ms(True)
-        # duplicate: append the selection, then rebuild (gaussian_viewer.py:323-327)
-        for name in ("_xyz", "_scaling", "_rotation", "_opacity", "_diffuse", "_normal", "_roughness", "_f0"):
-            t = getattr(pc, name)
-            extra = t[sel].clone()
-            if name == "_xyz":
-                extra += torch.tensor([0.0, 0.3, 0.0], device="cuda")
-            if name == "_opacity":
-                extra[:] = 2.0
-            setattr(pc, name, torch.cat([t, extra]))
+        # duplicate: append the selection (means offset), then rebuild (gaussian_viewer.py:323-327,
+        # editable_gaussian_model.py:284-322) -- one scan + one launch for all eight arrays (edit.duplicate)
+        names = ("_xyz", "_scaling", "_rotation", "_opacity", "_diffuse", "_normal", "_roughness", "_f0")
+        pc._opacity[sel] = 2.0  # (undo the delete so that the copy is visible)
+        torch.cuda.synchronize()
+        a = ev()  # the reference's op chain: per array `t[sel].clone()` (+ offset) and `torch.cat`
+        ref_new = [torch.cat((getattr(pc, n_), getattr(pc, n_)[sel].clone() + (torch.tensor([0.0, 0.3, 0.0], device="cuda") if n_ == "_xyz" else 0)))
+                   for n_ in names]
+        b = ev()
+        torch.cuda.synchronize()
+        res["duplicate_ms_torch_ops"] = a.elapsed_time(b)
+        del ref_new
+        a = ev()
+        new, extra = edit.duplicate([getattr(pc, n_) for n_ in names], sel, add_index=0, add_row=(0.0, 0.3, 0.0))
+        b = ev()
+        torch.cuda.synchronize()
+        res["duplicate_ms"] = a.elapsed_time(b)
+        res["duplicated_rows"] = extra
+        for n_, t in zip(names, new):
+            setattr(pc, n_, t)
         a = ev()
         rtr.rebuild_bvh()
         b = ev()
@@ -225,17 +236,19 @@ def c4(n4=3_000_000, steps=10, warmup=3):
     cams = scenes.kitchen_cameras(64, W, Hh)
     tg = scenes.random_targets(W, Hh, seed=3)
     views = [scenes.SyntheticCamera(c, tg, device=dev) for c in cams[:16]]
+    if world > 1:
+        distributed.use_registered_gradient_records()
     rtr = egr_b200.GaussianRaytracer(pc, W, Hh, ppll_forward_size=1000, ppll_backward_size=120_000_000)
     rt = rtr.cuda_module
     rt.get_config().num_bounces.fill_(1)
     g = rt.get_gaussians()
     rays = torch.zeros((), dtype=torch.int64, device=dev)
+    from egr_b200 import trainer as trainer_mod
+
+    tr = trainer_mod.Trainer(pc, rtr, pruning_interval=10 ** 9)  # render + all-reduce + fused optimiser step
 
     def step(i):
-        v = views[distributed.shard_views(len(views), rank, world, i)]
-        with torch.enable_grad():
-            egr_b200.render(v, rtr)
-        distributed.allreduce_gradients(g.grad_records)
+        tr.step(views[distributed.shard_views(len(views), rank, world, i)])
         rays.add_(rt.get_stats().num_steps_per_pixel.sum())
 
     for i in range(warmup):
@@ -259,10 +272,18 @@ def c4(n4=3_000_000, steps=10, warmup=3):
            "n_gpus": world, "ms_per_step": ms / steps, "views_per_s": world * steps / (ms * 1e-3),
            "mrays_s": int(rays.item()) / (ms * 1e-3) / 1e6, "hitlog_overflow": int(st.hitlog_status[2].item()),
            "hits_per_primary_ray": float(st.num_hits_per_pixel.sum().item()) / (W * Hh),
-           "pass": bool(torch.isfinite(g.grad_records).all()) and int(st.hitlog_status[2].item()) == 0}
+           "iteration": "render(view) + gradient all-reduce + fused Adam step (trainer.Trainer.step)",
+           "pass": bool(torch.isfinite(pc._xyz).all()) and int(st.hitlog_status[2].item()) == 0}
     if rank == 0:
         print(json.dumps(res))
     if world > 1:
+        del tr, rtr, rt, g, pc
+        import gc
+
+        gc.collect()
+        torch.cuda.synchronize()
+        distributed.release_registered_pools()
+        torch.cuda.empty_cache()
         dist.destroy_process_group()
 
 
