@@ -46,6 +46,19 @@ CONFIGS = {
 }
 
 
+def kernel_sources_sha256():
+    """Hash of the CUDA sources the library is built from (ties profiles/traffic.json to the kernels it was captured from)."""
+    import hashlib
+
+    from egr_b200 import build as _b
+
+    h = hashlib.sha256()
+    for f in sorted(_b.SOURCES + _b.HEADERS):
+        with open(os.path.join(_b.CSRC, f), "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()
+
+
 def make_scene(kind, n):
     from egr_b200 import scenes
 
@@ -370,8 +383,8 @@ def run_ours(args):
             try:
                 tj = json.load(open(tpath))
                 traffic = tj.get(dom)
-                if os.path.getmtime(_capi.lib_path()) > os.path.getmtime(tpath) + 1:
-                    traffic_note = "profiles/traffic.json is older than the library: capture predates the last kernel change"
+                if tj.get("kernel_sources_sha256") != kernel_sources_sha256():
+                    traffic_note = "profiles/traffic.json was captured from other kernel sources than the ones built now"
             except Exception:
                 traffic = None
         kname = {f"trace_step{s}": f"k_trace_step(step={s})" for s in range(S)}
