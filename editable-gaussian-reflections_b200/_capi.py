@@ -67,6 +67,7 @@ class EgrParams(C.Structure):
         ("hitlog", _FP), ("hitlog_bytes", C.c_size_t),
         ("used_ray_origin", _FP), ("used_ray_direction", _FP), ("step_executed", _FP),
         ("override_ray_origin", _FP), ("override_ray_direction", _FP), ("override_step_executed", _FP),
+        ("early_stop_transmittance", C.c_float), ("reserved1", C.c_uint32),
     ]
 
 

@@ -333,6 +333,7 @@ class Raytracer:
         p = _capi.EgrParams()
         p.image_width, p.image_height, p.num_steps = self.width, self.height, self._S
         p.tile_rows = getattr(self, "_tile_rows", 0)
+        p.early_stop_transmittance = float(getattr(self, "_early_stop", 0.0))
         for f in _capi.CAMERA_FIELDS:
             setattr(p.camera, f, getattr(self.camera_data, f).data_ptr())
         p.config = self._config_struct()
@@ -462,6 +463,17 @@ class Raytracer:
         g = self.gaussian_data
         _capi.check(self._lib.egr_gradients_accumulate(g.grad_records.data_ptr(), int(g.grad_records.shape[0]),
                                                        C.byref(t), self._stream()))
+
+    def set_early_stop(self, transmittance_threshold: float = 0.0):
+        """Opt-in early-stop mode (not in the reference; 0 = exact mode, the default).  With a threshold > 0 a ray stops
+        collecting hits once its composite has terminated and the running total transmittance is below the threshold:
+        ``output_total_transmittance`` is then within the threshold of the exact value, the composited radiance and
+        G-buffers are unchanged.  Meant for opaque scenes (trained models, novel-view rendering), where most of a ray's
+        Gaussians lie behind the surface it ends on."""
+        if not (0.0 <= float(transmittance_threshold) < 1.0):
+            raise RuntimeError("early-stop threshold must be in [0, 1)")
+        self._early_stop = float(transmittance_threshold)
+        self._build_params()
 
     def set_pixel_band(self, row_begin: int | None = None, row_end: int | None = None):
         """Restrict the following raytrace() calls to the pixel rows [row_begin, row_end) (``row_begin`` a multiple of 4,

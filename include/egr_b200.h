@@ -146,6 +146,13 @@ typedef struct EgrParams {       /* csrc/params.h:11-26 */
      * differences in a reflected ray are not amplified by the next step. */
     const float *override_ray_origin, *override_ray_direction;
     const int32_t *override_step_executed;
+    /* 0 (default): exact mode -- every hit along a ray is enumerated, total transmittance and hit lists are the
+     * reference's.  > 0 (opt-in, no counterpart in the reference): early-stop mode -- hits are collected nearest first
+     * and a ray stops collecting once its composite has terminated AND the running total transmittance is below this
+     * threshold; output_total_transmittance is then an upper bound within the threshold of the exact value, everything
+     * composited is unchanged (ties at exactly equal distance may be ordered differently).  For opaque scenes. */
+    float early_stop_transmittance;
+    uint32_t reserved1;
 } EgrParams;
 
 /* ---- library ------------------------------------------------------------------------------------------ */

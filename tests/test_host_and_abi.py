@@ -48,7 +48,7 @@ def test_struct_layout_matches_header():
     assert C.sizeof(_capi.EgrFramebuffer) == 25 * 8
     assert C.sizeof(_capi.EgrGaussians) == 8 + 9 * 8
     assert C.sizeof(_capi.EgrMetadata) == 3 * 8 and C.sizeof(_capi.EgrStats) == 6 * 8
-    assert C.sizeof(_capi.EgrParams) == 16 + (6 + 20 + 25 + 10 + 3 + 6) * 8 + 6 * 8 + 3 * 8 + 3 * 8  # ... + 3 debug outputs + 3 test inputs
+    assert C.sizeof(_capi.EgrParams) == 16 + (6 + 20 + 25 + 10 + 3 + 6) * 8 + 6 * 8 + 3 * 8 + 3 * 8 + 8  # ... + 3 debug outputs + 3 test inputs + early-stop threshold
 
 
 def test_size_queries_and_argument_errors_without_gpu():
