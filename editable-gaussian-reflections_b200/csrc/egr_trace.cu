@@ -207,6 +207,7 @@ constexpr uint32_t NO_LEAF = 0xFFFFFFFFu;
 #ifdef EGR_TASK_CLOCKS
 __shared__ uint32_t s_dbg_nodes[128], s_dbg_rounds[128];
 __shared__ long long s_dbg_tnode[4], s_dbg_tcand[4];
+__shared__ uint32_t s_dbg_outer[4], s_dbg_tsph[4];  // warp-level outer rounds | sum of max-lane survivors << 12; sphere-test cycles >> 6
 #define EGR_DBG_NODE() (s_dbg_nodes[threadIdx.x]++)
 #define EGR_DBG_ROUND() (s_dbg_rounds[threadIdx.x]++)
 #else
@@ -319,7 +320,7 @@ __device__ __forceinline__ void traverse_lane(
 #ifdef EGR_TASK_CLOCKS
         __syncwarp();
         const long long tb_ = clock64();
-        if ((threadIdx.x & 31) == 0) s_dbg_tnode[threadIdx.x >> 5] += tb_ - ta_;
+        if ((threadIdx.x & 31) == 0) s_dbg_tnode[threadIdx.x >> 5] += tb_ - ta_, s_dbg_outer[threadIdx.x >> 5]++;
 #endif
         for (int half = 0; half < 2; ++half) {
             if (half == 1) leaf = leaf2, leaf_n = leaf2_n;
@@ -332,6 +333,9 @@ __device__ __forceinline__ void traverse_lane(
             // part 1: the centre quads, EGR_QBATCH independent loads at a time, through the bounding-sphere test -> this
             // lane's own set of survivors
             uint32_t pass = 0;
+#ifdef EGR_TASK_CLOCKS
+            const long long ts_ = clock64();  // (only the lanes that hold a range are here)
+#endif
             for (uint32_t k0 = 0; k0 < leaf_n; k0 += EGR_QBATCH) {
                 float4 q[EGR_QBATCH];
 #pragma unroll
@@ -341,6 +345,14 @@ __device__ __forceinline__ void traverse_lane(
                 for (int i = 0; i < EGR_QBATCH; ++i)
                     if (k0 + i < leaf_n && sphere_pass(q[i], o, d)) pass |= 1u << (k0 + i);
             }
+#ifdef EGR_TASK_CLOCKS
+            {
+                const unsigned am_ = __activemask();
+                const uint32_t ms_ = __reduce_max_sync(am_, (uint32_t)__popc(pass));
+                if ((threadIdx.x & 31) == (uint32_t)(__ffs(am_) - 1))
+                    s_dbg_tsph[threadIdx.x >> 5] += (uint32_t)((clock64() - ts_) >> 6), s_dbg_outer[threadIdx.x >> 5] += ms_ << 12;
+            }
+#endif
             // part 2: exact tests of the survivors only, in leaf order: the warp runs max-over-lanes survivors
             // instead of one divergent body per candidate slot
             while (pass) {
@@ -812,7 +824,7 @@ __global__ void __launch_bounds__(32 * WARPS, (LANE_WALK ? EGR_LANE_WARPS : 20) 
         g += g_first;
 #ifdef EGR_TASK_CLOCKS
         s_dbg_nodes[threadIdx.x] = 0, s_dbg_rounds[threadIdx.x] = 0;
-        if (lane == 0) s_dbg_tnode[wib] = 0, s_dbg_tcand[wib] = 0;
+        if (lane == 0) s_dbg_tnode[wib] = 0, s_dbg_tcand[wib] = 0, s_dbg_outer[wib] = 0, s_dbg_tsph[wib] = 0;
         __syncwarp();
         const long long tc0_ = clock64();
         unsigned long long t0_;
@@ -836,7 +848,9 @@ __global__ void __launch_bounds__(32 * WARPS, (LANE_WALK ? EGR_LANE_WARPS : 20) 
             const long long tot_ = clock64() - tc0_;
             if (lane == 0 && g < 32768 && grads && c.hitlog_chunks >= 100000) {
                 dbg[g] = make_uint4((uint32_t)t0_, (uint32_t)(t1_ - t0_), nmax | (rmax << 16), nsum);
-                dbg[g + 65536] = make_uint4((uint32_t)(s_dbg_tnode[wib] >> 4), (uint32_t)(s_dbg_tcand[wib] >> 4), (uint32_t)(tot_ >> 4), 0);
+                dbg[g + 65536] = make_uint4((uint32_t)(s_dbg_tnode[wib] >> 4),
+                                            ((uint32_t)(s_dbg_tcand[wib] >> 4) & 0x1FFFFu) | (min(s_dbg_tsph[wib], 0x7FFFu) << 17),
+                                            (uint32_t)(tot_ >> 4), s_dbg_outer[wib]);
             }
             (void)sm_;
         }

@@ -52,7 +52,12 @@ for vi in (17,):
         nmax = d[:ng, 2] & 0xFFFF; rmax = d[:ng, 2] >> 16; nsum = d[:ng, 3]
         if s == 1:
             e = dbg2[s][:ng]
-            print(f"   cycles: node-walk {e[:,0].sum()/e[:,2].sum():.2f}  candidates {e[:,1].sum()/e[:,2].sum():.2f}  rest (select/composite/bounce) {1-(e[:,0].sum()+e[:,1].sum())/e[:,2].sum():.2f}")
+            ec = e[:, 1] & 0x1FFFF
+            print(f"   cycles: node-walk {e[:,0].sum()/e[:,2].sum():.2f}  candidates {ec.sum()/e[:,2].sum():.2f}  rest (select/composite/bounce) {1-(e[:,0].sum()+ec.sum())/e[:,2].sum():.2f}")
+            outer = e[:, 3] & 0xFFF; surv = e[:, 3] >> 12  # outer rounds; sum over range-halves of the max-lane survivor count
+            cyc_walk, cyc_cand, cyc_sph = e[:, 0] * 16.0, (e[:, 1] & 0x1FFFF) * 16.0, (e[:, 1] >> 17) * 64.0
+            print(f"   warp-level outer rounds per task: mean={outer.mean():.1f} max={outer.max()}; max-lane survivors per round: {surv.sum()/max(outer.sum(),1):.1f}")
+            print(f"   cycles per outer round: walk {cyc_walk.sum()/max(outer.sum(),1):.0f}  candidates {cyc_cand.sum()/max(outer.sum(),1):.0f} (of which sphere tests {cyc_sph.sum()/max(outer.sum(),1):.0f});  cycles per max-lane exact test {(cyc_cand.sum()-cyc_sph.sum())/max(surv.sum(),1):.0f}")
             print(f"   lane node visits per task: max-lane mean={nmax.mean():.0f} p99={np.percentile(nmax,99):.0f} max={nmax.max()}; lane-sum mean={nsum.mean():.0f}; leaf rounds max-lane mean={rmax.mean():.1f} max={rmax.max()}")
             cc = np.corrcoef(nmax, dt)[0,1]; print(f"   corr(dur, nmax)={cc:.2f}; ns per max-lane node visit: median={np.median(dt/np.maximum(nmax,1)):.0f}")
             order = np.argsort(-dt)[:5]
